@@ -1,0 +1,149 @@
+/* minnow_cuda.h -- C ABI of libminnow_cuda.so: the B200 (sm_100a)
+ * implementation of minnow's encode/decode hot path, registered as algorithm
+ * `algo_Diff` v0.9 behind the reference's plugin interface.
+ *
+ * Plain C: pointers, sizes, the reference's own by-value structs. No torch,
+ * no C++ types. Every entry point cites the reference interface it replaces
+ * (paths under /root/reference). There is no CPU fallback: every entry point
+ * needs a CUDA device and aborts (Panic convention, src/debug.h:72-89) on a
+ * CUDA failure.
+ */
+#ifndef MINNOW_CUDA_H_
+#define MINNOW_CUDA_H_
+
+#include <stdint.h>
+#include "minnow_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MNWCUDA_ALGO_CODE    algo_Diff
+#define MNWCUDA_ALGO_VERSION 0x00000900u /* 0.9.0-dev, src/semver.c:93-94 */
+
+#define MNWCUDA_BLOCK_LEN    1024 /* values per pack block */
+#define MNWCUDA_DITHER_RUN   32   /* consecutive blocks per dither task */
+#define MNWCUDA_DITHER_LANES 32   /* rand_Seed streams per dither task */
+
+/* ---- wire structs of the Diff v0.9 payload (CField.Data) ---- */
+typedef struct MnwDiffHeader { /* 64 bytes, little-endian; the pointer-free
+                                  image of Position/VelocityQuantization
+                                  (src/types.h:82-95) */
+    uint32_t Magic;       /* algo_Diff */
+    uint32_t Version;     /* MNWCUDA_ALGO_VERSION */
+    uint32_t FieldCode;
+    int32_t  ParticleLen;
+    uint8_t  Depth;
+    uint8_t  Pad[3];
+    float    Width;       /* Posn: box width; Velc: SymLog10Threshold (0) */
+    float    X0[3];
+    float    X1[3];
+    uint32_t BlockLen;
+    uint16_t DitherRun;
+    uint16_t DitherLanes;
+    uint64_t DitherSeed;
+} MnwDiffHeader;
+
+typedef struct MnwDiffBlock { /* 16 bytes per block, table follows the header */
+    uint32_t First;
+    int32_t  MinDelta;
+    uint32_t Width;
+    uint32_t Offset16;
+} MnwDiffBlock;
+
+/* ---- one field of a batch (host array) ---- */
+typedef struct MnwFieldDesc {
+    int64_t  Offset;     /* encode: first float of the field's 3N planar input
+                            inside d_in; decode: same inside d_out */
+    int32_t  ParticleLen;
+    uint32_t FieldCode;  /* field_Posn or field_Velc (src/types.h:8-9) */
+    float    Delta;      /* Position/VelocityAccuracy.Delta (types.h:42-55) */
+    float    Width;      /* PositionAccuracy.Width; ignored for Velc */
+    uint64_t DitherSeed; /* recorded in the header; the decoder's rand_Seed seed
+                            (replaces clock() of src/quant.c:639) */
+} MnwFieldDesc;
+
+typedef struct MnwCudaCtx MnwCudaCtx;
+
+/* ---- sizes (host arithmetic only) ---- */
+int64_t mnwcuda_FieldFixedBytes(int32_t particleLen); /* header + block table */
+int64_t mnwcuda_FieldBound(int32_t particleLen);      /* worst-case payload */
+
+/* ---- context: device scratch, stream-ordered; one per thread ----
+ * The algorithm-private `void *Buffer` of the plugin interface
+ * (src/types.h:133, src/register.h:15-22) is one of these. */
+MnwCudaCtx *mnwcuda_Create(int device);
+void mnwcuda_Destroy(MnwCudaCtx *ctx);
+
+/* ---- device-resident batch entry points (the timed path) ----
+ * Replace, for every field of the batch at once,
+ *   encode: quant_QField (src/quant.c:135-144 -> position()/velocity()
+ *           :161-289: util_UndoPeriodic, util_MinMax, deltaToDepth,
+ *           util_UniformBinIndex) followed by CFunc (src/funcs.c:71)
+ *   decode: DFunc (src/funcs.c:54) followed by quant_Field
+ *           (src/quant.c:146-155 -> undoPosition()/undoVelocity() :451-551:
+ *           util_UndoUniformBinIndex, util_Periodic).
+ * d_in/d_out/d_offsets are device pointers; h_fields is a host array.
+ * Field f's payload is d_out[d_offsets[f] .. d_offsets[f+1]); d_offsets has
+ * nFields+1 entries. `stream` is a cudaStream_t (NULL = default stream).
+ * Work is enqueued, not waited for. Returns 0, or <0 for a host-side
+ * argument error; device-side errors are reported by mnwcuda_Status. */
+int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in,
+                            const MnwFieldDesc *h_fields, int64_t nFields,
+                            uint8_t *d_out, int64_t outCap,
+                            uint64_t *d_offsets, void *stream);
+int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in,
+                            const uint64_t *d_offsets,
+                            const MnwFieldDesc *h_fields, int64_t nFields,
+                            float *d_out, void *stream);
+/* Waits for `stream` and returns 0 or the first device-side error of the
+ * calls since the last Status: 1 = accuracy needs depth > 24 (the Panic of
+ * src/quant.c:688-693), 2 = output capacity exceeded, 3 = malformed payload. */
+int mnwcuda_Status(MnwCudaCtx *ctx, void *stream);
+/* Kernels launched by this context since creation (bench bookkeeping). */
+int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx);
+
+/* ---- host-buffer entry points (reference-facing, synchronous) ----
+ * mnwcuda_EncodeField == CFunc(quant_QField(f)); the returned CField.Data is
+ * malloc'd and released by the caller with free() (CSeg_Free,
+ * src/funcs.c:205-210); Checksum is left 0 for the caller (src/types.h:135).
+ * mnwcuda_DecodeField == quant_Field(DFunc(cf)); Data and Acc are malloc'd
+ * (quant_FreeField, src/quant.c:100-113). `buffer` is a MnwCudaCtx*. */
+CField mnwcuda_EncodeField(Field f, void *buffer);
+Field mnwcuda_DecodeField(CField cf, void *buffer);
+/* Many fields per call with host buffers: H2D, kernels and D2H are pipelined
+ * over chunks of fields. h_in holds the fields' floats at h_fields[i].Offset;
+ * payloads are written back to back into h_out, h_offsets[nFields+1]. Returns
+ * total bytes or <0. */
+int64_t mnwcuda_EncodeFieldsHost(MnwCudaCtx *ctx, const float *h_in,
+                                 const MnwFieldDesc *h_fields, int64_t nFields,
+                                 uint8_t *h_out, int64_t outCap,
+                                 uint64_t *h_offsets);
+int mnwcuda_DecodeFieldsHost(MnwCudaCtx *ctx, const uint8_t *h_in,
+                             const uint64_t *h_offsets,
+                             const MnwFieldDesc *h_fields, int64_t nFields,
+                             float *h_out);
+
+/* ---- the six plugin functions (src/register.h:15-22; shape of
+ * src/algo_Test_v0_9.h:6-13). CFunc takes quantized uint64 values and a
+ * Position/VelocityQuantization in qf.Quant; DFunc returns them. ---- */
+CField MnwCudaCompress_v0_9(QField qf, void *buffer);
+QField MnwCudaDecompress_v0_9(CField cf, void *buffer);
+void *MnwCudaCAlloc_v0_9(void);
+void MnwCudaCFree_v0_9(void *buffer);
+void *MnwCudaDAlloc_v0_9(void);
+void MnwCudaDFree_v0_9(void *buffer);
+/* Dither seed used by EncodeField / Compress on this buffer (default 0). */
+void mnwcuda_SetDitherSeed(void *buffer, uint64_t seed);
+
+/* ---- synthetic input (bench/tests): Zel'dovich-displaced Lagrangian grid,
+ * ids [firstId, firstId+count) of an ngrid^3 box, planar float32.
+ * d_pos / d_vel may be NULL. ---- */
+int mnwcuda_GenerateZeldovich(MnwCudaCtx *ctx, int32_t ngrid, float boxWidth,
+                              uint64_t seed, int64_t firstId, int64_t count,
+                              float *d_pos, float *d_vel, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINNOW_CUDA_H_ */

@@ -1,0 +1,310 @@
+"""minnow_c_b200 -- Python driver over libminnow_cuda.so (ctypes).
+
+The product is the C-ABI library (include/minnow_cuda.h); this package only
+loads it for tests and benchmarks and mirrors the reference's names
+(Field / CField / QField, Compress / Decompress, see /root/reference/src/
+types.h and funcs.h). torch is used for device memory and streams only.
+
+There is no CPU path: importing works anywhere (so the symbol table can be
+checked), but every compute call needs the built library and a CUDA device and
+raises loudly otherwise.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "libminnow_cuda.so")
+HOST_LIB_PATH = os.path.join(_HERE, "libminnow_host.so")
+
+FIELD_POSN = 0x506F736E
+FIELD_VELC = 0x56656C63
+ALGO_DIFF = 0x44696666
+ALGO_VERSION = 0x00000900
+BLOCK_LEN = 1024
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-fmad=false",
+    "-prec-div=true", "-prec-sqrt=true", "-ftz=false", "-lineinfo", "--extended-lambda",
+    "-shared", "-Xcompiler", "-fPIC",
+]
+
+
+def build(verbose=False):
+    """Compile libminnow_cuda.so for sm_100a (cross-compiles without a GPU)."""
+    src = os.path.join(_HERE, "csrc", "minnow_cuda.cu")
+    deps = [os.path.join(_HERE, "csrc", f) for f in os.listdir(os.path.join(_HERE, "csrc"))]
+    deps += [os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include"))]
+    if os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
+        return LIB_PATH
+    cmd = ["nvcc"] + NVCC_FLAGS + ["-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(_HERE, "csrc"),
+                                   "-o", LIB_PATH, src]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+# ---- ctypes images of the boundary structs (include/minnow_types.h) ----
+class FieldHeader(C.Structure):
+    _fields_ = [("FieldCode", C.c_uint32), ("AlgoCode", C.c_uint32), ("AlgoVersion", C.c_uint32),
+                ("ParticleLen", C.c_int32)]
+
+
+class Field(C.Structure):
+    _fields_ = [("Hd", FieldHeader), ("Valid", C.c_int64), ("Data", C.c_void_p), ("Acc", C.c_void_p)]
+
+
+class QField(C.Structure):
+    _fields_ = [("Hd", FieldHeader), ("Valid", C.c_int64), ("Data", C.c_void_p), ("Quant", C.c_void_p)]
+
+
+class CField(C.Structure):
+    _fields_ = [("Hd", FieldHeader), ("Data", C.c_void_p), ("DataLen", C.c_int64), ("Checksum", C.c_uint32)]
+
+
+class PositionAccuracy(C.Structure):
+    _fields_ = [("Deltas", C.c_void_p), ("Delta", C.c_float), ("Width", C.c_float), ("Len", C.c_int32)]
+
+
+class VelocityAccuracy(C.Structure):
+    _fields_ = [("Deltas", C.c_void_p), ("Delta", C.c_float), ("Len", C.c_int32),
+                ("SymLog10Scaled", C.c_int32), ("SymLog10Threshold", C.c_float)]
+
+
+class PositionQuantization(C.Structure):
+    _fields_ = [("Depths", C.c_void_p), ("Len", C.c_int32), ("Width", C.c_float), ("X0", C.c_float * 3),
+                ("X1", C.c_float * 3), ("Depth", C.c_uint8)]
+
+
+class VelocityQuantization(C.Structure):
+    _fields_ = [("Depths", C.c_void_p), ("Len", C.c_int32), ("SymLog10Scaled", C.c_int32),
+                ("X0", C.c_float * 3), ("X1", C.c_float * 3), ("SymLog10Threshold", C.c_float),
+                ("Depth", C.c_uint8)]
+
+
+class FieldDesc(C.Structure):
+    _fields_ = [("Offset", C.c_int64), ("ParticleLen", C.c_int32), ("FieldCode", C.c_uint32),
+                ("Delta", C.c_float), ("Width", C.c_float), ("DitherSeed", C.c_uint64)]
+
+
+EXPORTS = {
+    "mnwcuda_FieldFixedBytes": (C.c_int64, [C.c_int32]),
+    "mnwcuda_FieldBound": (C.c_int64, [C.c_int32]),
+    "mnwcuda_Create": (C.c_void_p, [C.c_int]),
+    "mnwcuda_Destroy": (None, [C.c_void_p]),
+    "mnwcuda_EncodeFieldsDev": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64, C.c_void_p,
+                                          C.c_int64, C.c_void_p, C.c_void_p]),
+    "mnwcuda_DecodeFieldsDev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64,
+                                          C.c_void_p, C.c_void_p]),
+    "mnwcuda_Status": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "mnwcuda_LaunchCount": (C.c_int64, [C.c_void_p]),
+    "mnwcuda_EncodeField": (CField, [Field, C.c_void_p]),
+    "mnwcuda_DecodeField": (Field, [CField, C.c_void_p]),
+    "mnwcuda_EncodeFieldsHost": (C.c_int64, [C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64, C.c_void_p,
+                                             C.c_int64, C.c_void_p]),
+    "mnwcuda_DecodeFieldsHost": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64,
+                                           C.c_void_p]),
+    "MnwCudaCompress_v0_9": (CField, [QField, C.c_void_p]),
+    "MnwCudaDecompress_v0_9": (QField, [CField, C.c_void_p]),
+    "MnwCudaCAlloc_v0_9": (C.c_void_p, []),
+    "MnwCudaCFree_v0_9": (None, [C.c_void_p]),
+    "MnwCudaDAlloc_v0_9": (C.c_void_p, []),
+    "MnwCudaDFree_v0_9": (None, [C.c_void_p]),
+    "mnwcuda_SetDitherSeed": (None, [C.c_void_p, C.c_uint64]),
+    "mnwcuda_GenerateZeldovich": (C.c_int, [C.c_void_p, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64,
+                                            C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+_lib = None
+_libc = C.CDLL(None)
+_libc.free.argtypes = [C.c_void_p]
+
+
+def lib():
+    """The loaded libminnow_cuda.so. Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libminnow_cuda.so is not built (run __graft_entry__.build()); "
+                               "there is no CPU fallback")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in EXPORTS.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def field_bound(n):
+    return lib().mnwcuda_FieldBound(n)
+
+
+def field_fixed_bytes(n):
+    return lib().mnwcuda_FieldFixedBytes(n)
+
+
+def make_descs(fields):
+    """fields: iterable of (offset, n, field_code, delta, width, seed)."""
+    fields = list(fields)
+    arr = (FieldDesc * max(len(fields), 1))()
+    for i, (off, n, code, delta, width, seed) in enumerate(fields):
+        arr[i] = FieldDesc(off, n, code, delta, width, seed)
+    return arr
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(stream)
+
+
+class Codec:
+    """One MnwCudaCtx: device scratch + the entry points, numpy/torch friendly."""
+
+    def __init__(self, device=None):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("minnow_c_b200 needs a CUDA device; there is no CPU fallback")
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = int(device)
+        self.ctx = lib().mnwcuda_Create(self.device)
+        if not self.ctx:
+            raise RuntimeError("mnwcuda_Create failed")
+
+    def close(self):
+        if self.ctx:
+            lib().mnwcuda_Destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return lib().mnwcuda_LaunchCount(self.ctx)
+
+    # ---- device-resident batch path ----
+    def encode_dev(self, d_in, descs, n_fields, d_out, d_offsets, stream=None):
+        rc = lib().mnwcuda_EncodeFieldsDev(self.ctx, d_in.data_ptr(), descs, n_fields, d_out.data_ptr(),
+                                           d_out.numel() * d_out.element_size(), d_offsets.data_ptr(),
+                                           _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwcuda_EncodeFieldsDev: %d" % rc)
+
+    def decode_dev(self, d_in, d_offsets, descs, n_fields, d_out, stream=None):
+        rc = lib().mnwcuda_DecodeFieldsDev(self.ctx, d_in.data_ptr(), d_offsets.data_ptr(), descs, n_fields,
+                                           d_out.data_ptr(), _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwcuda_DecodeFieldsDev: %d" % rc)
+
+    def status(self, stream=None):
+        return lib().mnwcuda_Status(self.ctx, _stream_ptr(stream))
+
+    def generate(self, ngrid, box, seed, first_id, count, d_pos=None, d_vel=None, stream=None):
+        rc = lib().mnwcuda_GenerateZeldovich(self.ctx, ngrid, box, seed, first_id, count,
+                                             d_pos.data_ptr() if d_pos is not None else None,
+                                             d_vel.data_ptr() if d_vel is not None else None,
+                                             _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwcuda_GenerateZeldovich: %d" % rc)
+
+    # ---- host-buffer batch path ----
+    def encode_host(self, h_in, descs, n_fields, h_out, h_offsets):
+        total = lib().mnwcuda_EncodeFieldsHost(self.ctx, _host_ptr(h_in), descs, n_fields, _host_ptr(h_out),
+                                               _host_nbytes(h_out), _host_ptr(h_offsets))
+        if total < 0:
+            raise ValueError("mnwcuda_EncodeFieldsHost: %d" % total)
+        return total
+
+    def decode_host(self, h_in, h_offsets, descs, n_fields, h_out):
+        rc = lib().mnwcuda_DecodeFieldsHost(self.ctx, _host_ptr(h_in), _host_ptr(h_offsets), descs, n_fields,
+                                            _host_ptr(h_out))
+        if rc:
+            raise ValueError("mnwcuda_DecodeFieldsHost: %d" % rc)
+
+    # ---- reference-shaped single-field calls (host numpy in/out) ----
+    def set_dither_seed(self, seed):
+        lib().mnwcuda_SetDitherSeed(self.ctx, seed)
+
+    def encode_field(self, field_code, data, delta, width=0.0):
+        """mnwcuda_EncodeField: float field (3N planar) -> payload bytes (numpy uint8)."""
+        data = np.ascontiguousarray(data, dtype=np.float32).reshape(-1)
+        n = data.size // 3
+        if field_code == FIELD_POSN:
+            acc = PositionAccuracy(None, delta, width, 0)
+        else:
+            acc = VelocityAccuracy(None, delta, 0, 0, 0.0)
+        f = Field(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), 1, data.ctypes.data, C.addressof(acc))
+        cf = lib().mnwcuda_EncodeField(f, self.ctx)
+        out = np.ctypeslib.as_array(C.cast(cf.Data, C.POINTER(C.c_uint8)), shape=(cf.DataLen,)).copy()
+        _libc.free(cf.Data)
+        return out
+
+    def decode_field(self, field_code, n, payload):
+        """mnwcuda_DecodeField: payload -> (floats[3N], reported Delta)."""
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        cf = CField(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), payload.ctypes.data, payload.size, 0)
+        f = lib().mnwcuda_DecodeField(cf, self.ctx)
+        if n:
+            out = np.ctypeslib.as_array(C.cast(f.Data, C.POINTER(C.c_float)), shape=(3 * n,)).copy()
+        else:
+            out = np.zeros(0, np.float32)
+        if field_code == FIELD_POSN:
+            delta = C.cast(f.Acc, C.POINTER(PositionAccuracy)).contents.Delta
+        else:
+            delta = C.cast(f.Acc, C.POINTER(VelocityAccuracy)).contents.Delta
+        _libc.free(f.Data)
+        _libc.free(f.Acc)
+        return out, delta
+
+    def compress(self, field_code, q64, x0, x1, depth, width=0.0):
+        """MnwCudaCompress_v0_9: the literal CFunc(QField) boundary."""
+        q64 = np.ascontiguousarray(q64, dtype=np.uint64)
+        n = q64.size // 3
+        if field_code == FIELD_POSN:
+            quant = PositionQuantization(None, 0, width, (C.c_float * 3)(*x0), (C.c_float * 3)(*x1), depth)
+        else:
+            quant = VelocityQuantization(None, 0, 0, (C.c_float * 3)(*x0), (C.c_float * 3)(*x1), 0.0, depth)
+        qf = QField(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), 1, q64.ctypes.data, C.addressof(quant))
+        cf = lib().MnwCudaCompress_v0_9(qf, self.ctx)
+        out = np.ctypeslib.as_array(C.cast(cf.Data, C.POINTER(C.c_uint8)), shape=(cf.DataLen,)).copy()
+        _libc.free(cf.Data)
+        return out
+
+    def decompress(self, field_code, n, payload):
+        """MnwCudaDecompress_v0_9: the literal DFunc(CField) boundary -> (q64, quant dict)."""
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        cf = CField(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), payload.ctypes.data, payload.size, 0)
+        qf = lib().MnwCudaDecompress_v0_9(cf, self.ctx)
+        q = np.ctypeslib.as_array(C.cast(qf.Data, C.POINTER(C.c_uint64)), shape=(3 * n,)).copy() if n else \
+            np.zeros(0, np.uint64)
+        cls = PositionQuantization if field_code == FIELD_POSN else VelocityQuantization
+        qt = C.cast(qf.Quant, C.POINTER(cls)).contents
+        info = {"X0": list(qt.X0), "X1": list(qt.X1), "Depth": int(qt.Depth)}
+        if field_code == FIELD_POSN:
+            info["Width"] = float(qt.Width)
+        _libc.free(qf.Data)
+        _libc.free(qf.Quant)
+        return q, info
+
+
+def _host_ptr(a):
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    return a.ctypes.data
+
+
+def _host_nbytes(a):
+    if hasattr(a, "data_ptr"):
+        return a.numel() * a.element_size()
+    return a.nbytes

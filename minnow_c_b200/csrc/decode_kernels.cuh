@@ -1,0 +1,281 @@
+// decode_kernels.cuh -- K3p header parse, K3a dither stream states, K3
+// unpack + inverse delta + dithered de-quantisation. Replaces, per field, the
+// (stub) DFunc behind /root/reference/src/funcs.c:54 and undoPosition()/
+// undoVelocity() of src/quant.c:451-551, with the dither arithmetic of
+// util_UndoUniformBinIndex (src/util.c:223-242) and the RNG of src/rand.c.
+#pragma once
+
+#include "minnow_kernels.cuh"
+
+namespace mnw {
+
+struct DecodeParams {
+    const uint8_t *in;
+    const uint64_t *offsets;  // [nFields+1]
+    const DevField *fields;
+    int nFields;
+    int uniformTasks;  // >0: every field has this many tasks
+    DevQuant *quant;   // [nFields] parsed from the headers
+    uint64_t *seeds;   // [nFields]
+    int *tableOf;      // [nFields] field whose stream table this field uses
+    uint64_t *states;  // [nFields][maxStreams][2]
+    int64_t maxStreams;
+    const uint64_t *jumpPow;  // [kJumpPows][128][2]: columns of J^(2^k)
+    float *out;
+    uint64_t *qOut;  // literal DFunc boundary: quantised values out, or null
+    int *error;
+};
+
+constexpr int kJumpPows = 26;
+
+// ---------------------------------------------------------------------------
+// K3p: one thread per field reads the 64-byte header: quantisation parameters,
+// seed, consistency checks; decides whose stream table to use (fields with the
+// seed of field 0 share table 0).
+// ---------------------------------------------------------------------------
+__global__ void k_parse_headers(DecodeParams p) {
+    int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= p.nFields) return;
+    const DevField fd = p.fields[f];
+    const uint8_t *src = p.in + p.offsets[f];
+    __align__(16) MnwDiffHeader h;
+    for (int i = 0; i < 4; i++)
+        reinterpret_cast<uint4 *>(&h)[i] = reinterpret_cast<const uint4 *>(src)[i];
+    bool ok = h.Magic == algo_Diff && h.ParticleLen == fd.n && h.BlockLen == kBlockLen &&
+              h.DitherRun == MNWCUDA_DITHER_RUN && h.DitherLanes == MNWCUDA_DITHER_LANES &&
+              h.Depth <= 24 && h.FieldCode == fd.fieldCode;
+    if (!ok) atomicCAS(p.error, 0, kErrPayload);
+    DevQuant q;
+    float md = 0.0f;
+    for (int c = 0; c < 3; c++) {
+        q.X0[c] = h.X0[c];
+        q.X1[c] = h.X1[c];
+        float d = __fsub_rn(h.X1[c], h.X0[c]);
+        if (md < d) md = d;
+    }
+    q.maxDiff = md;
+    q.depth = ok ? h.Depth : 0xffffffffu;
+    p.quant[f] = q;
+    p.seeds[f] = h.DitherSeed;
+    const MnwDiffHeader *h0 = reinterpret_cast<const MnwDiffHeader *>(p.in + p.offsets[0]);
+    int64_t mine = (3 * (int64_t)fd.nb + kRun - 1) / kRun * 32;
+    int64_t zero = (3 * (int64_t)p.fields[0].nb + kRun - 1) / kRun * 32;
+    p.tableOf[f] = (h.DitherSeed == h0->DitherSeed && mine <= zero) ? 0 : f;
+}
+
+// splitmix64, src/rand.c:114-121
+__device__ __forceinline__ uint64_t splitmix_next(uint64_t &s) {
+    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// ---------------------------------------------------------------------------
+// K3a: rand_Seed(seed, nStreams) (src/rand.c:22-39) in parallel. Stream k is
+// the seed state advanced by k jumps of 2^64 draws; the jump is GF(2)-linear,
+// so J^k s = product over the set bits of k of the precomputed J^(2^i), each
+// applied as an XOR of the matrix columns selected by the state's bits.
+// One thread per stream; only fields that own a table do work.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_stream_states(DecodeParams p) {
+    int f = blockIdx.y;
+    if (p.tableOf[f] != f) return;
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const DevField fd = p.fields[f];
+    int64_t nStreams = (3 * (int64_t)fd.nb + kRun - 1) / kRun * 32;
+    if (k >= nStreams) return;
+    uint64_t sm = p.seeds[f];
+    uint64_t s0 = splitmix_next(sm);
+    uint64_t s1 = splitmix_next(sm);
+    for (int bit = 0; bit < kJumpPows; bit++) {
+        if (!((k >> bit) & 1)) continue;
+        const ulonglong2 *col = reinterpret_cast<const ulonglong2 *>(p.jumpPow) + bit * 128;
+        uint64_t a = 0, b = 0;
+#pragma unroll 8
+        for (int i = 0; i < 64; i++) {
+            ulonglong2 c0 = __ldg(col + i);
+            ulonglong2 c1 = __ldg(col + 64 + i);
+            uint64_t m0 = 0ull - ((s0 >> i) & 1ull);
+            uint64_t m1 = 0ull - ((s1 >> i) & 1ull);
+            a ^= (c0.x & m0) ^ (c1.x & m1);
+            b ^= (c0.y & m0) ^ (c1.y & m1);
+        }
+        s0 = a;
+        s1 = b;
+    }
+    uint64_t *dst = p.states + ((int64_t)f * p.maxStreams + k) * 2;
+    dst[0] = s0;
+    dst[1] = s1;
+}
+
+// ---------------------------------------------------------------------------
+// K3: one warp per dither task = 32 consecutive blocks of one field; lane l
+// owns stream task*32+l and values [32l, 32l+32) of every block it visits.
+//   unpack  util_U32UndoUniformPack (src/util.c:383-403): coalesced word
+//           loads staged through skewed shared memory, lane reads its `width`
+//           words and shifts its 32 residuals out
+//   scan    q[j] = first + sum_{i<=j} (r[i]+minDelta): lane-local inclusive
+//           sums + warp shuffle scan of the lane totals
+//   dequant util_UndoUniformBinIndex (src/util.c:229-238), two separately
+//           rounded statements, one xorshift128+ draw per value
+//   wrap    util_Periodic (src/util.c:76-82), Posn only
+//   store   transposed through swizzled shared memory, 128-bit coalesced
+// ---------------------------------------------------------------------------
+constexpr int kDecWarps = 4;
+
+template <bool kToQ>
+__global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
+    __shared__ __align__(16) uint32_t stage[kDecWarps][kStageWords];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t task = (int64_t)blockIdx.x * kDecWarps + warp;
+    if (task >= nTasksTotal) return;
+    uint32_t *st = stage[warp];
+
+    int f;
+    if (p.uniformTasks > 0) {
+        f = (int)(task / p.uniformTasks);
+    } else {
+        const DevField *fields = p.fields;
+        f = find_field(p.nFields, task, [fields](int i) { return fields[i].firstTask; });
+    }
+    const DevField fd = p.fields[f];
+    const DevQuant qp = p.quant[f];
+    if (qp.depth > 24) return;  // malformed header, error already raised
+    const int localTask = (int)(task - fd.firstTask);
+    const uint8_t *region = p.in + p.offsets[f];
+    const int64_t regionLen = (int64_t)(p.offsets[f + 1] - p.offsets[f]);
+    const uint4 *table = reinterpret_cast<const uint4 *>(region + 64);
+    const int64_t fixed = 64 + (int64_t)fd.nb * 48;
+    const uint32_t *payload = reinterpret_cast<const uint32_t *>(region + fixed);
+
+    uint64_t s0 = 0, s1 = 0;
+    if (!kToQ) {
+        const uint64_t *sp =
+            p.states + ((int64_t)p.tableOf[f] * p.maxStreams + (int64_t)localTask * 32 + lane) * 2;
+        s0 = sp[0];
+        s1 = sp[1];
+    }
+    const bool isPos = fd.fieldCode == field_Posn;
+    const float L = fd.width;
+    const float bw = __fdiv_rn(qp.maxDiff, (float)(1u << qp.depth));
+
+    const int gEnd = min(3 * fd.nb, (localTask + 1) * kRun);
+    for (int g = localTask * kRun; g < gEnd; g++) {
+        const int comp = g / fd.nb;
+        const int b = g - comp * fd.nb;
+        const int len = min(kBlockLen, fd.n - b * kBlockLen);
+        const uint4 e = __ldg(table + g);
+        const uint32_t first = e.x;
+        const uint32_t minDelta = e.y;
+        const int w = (int)e.z;
+        const int nWords = (len * w + 31) >> 5;
+        const uint32_t *src = payload + (int64_t)e.w * 4;
+        if (w > kMaxWidth || fixed + (int64_t)e.w * 16 + (int64_t)nWords * 4 > regionLen) {
+            if (lane == 0) atomicCAS(p.error, 0, kErrPayload);
+            return;
+        }
+
+        // ---- unpack ----
+        for (int m = lane; m < nWords; m += 32) st[skew(m)] = __ldg(src + m);
+        __syncwarp();
+        uint32_t r[kChunk];
+        if (w > 0) {
+            const uint32_t mask = (1u << w) - 1u;
+            uint64_t acc = 0;
+            int fill = 0, wi = lane * w;
+#pragma unroll
+            for (int i = 0; i < kChunk; i++) {
+                if (fill < w) {
+                    uint32_t word = wi < nWords ? st[skew(wi)] : 0u;
+                    wi++;
+                    acc |= (uint64_t)word << fill;
+                    fill += 32;
+                }
+                r[i] = (uint32_t)acc & mask;
+                acc >>= w;
+                fill -= w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < kChunk; i++) r[i] = 0;
+        }
+        __syncwarp();
+
+        // ---- inverse delta: inclusive scan of d, d[0] := 0 ----
+        uint32_t run = 0;
+#pragma unroll
+        for (int i = 0; i < kChunk; i++) {
+            uint32_t d = r[i] + minDelta;
+            if (lane == 0 && i == 0) d = 0;
+            run += d;
+            r[i] = run;
+        }
+        uint32_t incl = run;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += up;
+        }
+        const uint32_t base = first + (incl - run);
+
+        if (kToQ) {
+            // literal DFunc boundary: uint64 quantised values out
+            uint64_t *dst = p.qOut + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
+#pragma unroll
+            for (int i = 0; i < kChunk; i++) st[skew(lane * kChunk + i)] = base + r[i];
+            __syncwarp();
+#pragma unroll 4
+            for (int k = 0; k < 32; k++) {
+                int el = k * 32 + lane;
+                if (el < len) dst[el] = st[skew(el)];
+            }
+            __syncwarp();
+            continue;
+        }
+
+        // ---- dither + de-quantise + wrap, into swizzled staging ----
+        const float x0 = qp.X0[comp];
+        float *sf = reinterpret_cast<float *>(st);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            float o[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int idx = j * 4 + i;
+                float v = 0.0f;
+                if (lane * kChunk + idx < len) {
+                    uint32_t qv = base + r[idx];
+                    float edge = __fadd_rn(x0, __fmul_rn(bw, (float)qv));
+                    uint32_t bits = (uint32_t)xs128p_next(s0, s1) & 0xffffffu;
+                    float u = __fmul_rn((float)bits, 5.9604644775390625e-08f);  // /2^24, exact
+                    v = __fadd_rn(edge, __fmul_rn(u, bw));
+                    if (isPos) v = wrap(v, L);
+                }
+                o[i] = v;
+            }
+            reinterpret_cast<float4 *>(sf)[swz_chunk(lane, j)] = make_float4(o[0], o[1], o[2], o[3]);
+        }
+        __syncwarp();
+
+        // ---- coalesced store ----
+        float *dst = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
+        if (len == kBlockLen && ((uintptr_t)dst & 15) == 0) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                int c = k * 32 + lane;
+                float4 v = reinterpret_cast<const float4 *>(sf)[swz_chunk(c >> 3, c & 7)];
+                __stcs(reinterpret_cast<float4 *>(dst) + c, v);
+            }
+        } else {
+#pragma unroll 4
+            for (int k = 0; k < 32; k++) {
+                int el = k * 32 + lane;
+                if (el < len) dst[el] = sf[swz_chunk(el >> 5, (el >> 2) & 7) * 4 + (el & 3)];
+            }
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace mnw

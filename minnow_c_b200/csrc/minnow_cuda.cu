@@ -1,0 +1,756 @@
+// minnow_cuda.cu -- host side of libminnow_cuda.so: the extern "C" ABI of
+// include/minnow_cuda.h over the kernels in encode_kernels.cuh /
+// decode_kernels.cuh / gen_kernels.cuh. sm_100a only; build with
+//   nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo -O3
+// There is no CPU path: without a device every entry point aborts.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "minnow_cuda.h"
+#include "decode_kernels.cuh"
+#include "encode_kernels.cuh"
+#include "gen_kernels.cuh"
+
+using namespace mnw;
+
+// Panic convention of /root/reference/src/debug.h:72-89: message, exit(1).
+#define CUDA_CHECK(expr)                                                                 \
+    do {                                                                                 \
+        cudaError_t err_ = (expr);                                                       \
+        if (err_ != cudaSuccess) {                                                       \
+            fprintf(stderr, "Panic at file %s, line %d:\nCUDA error %s: %s\n", __FILE__, \
+                    __LINE__, cudaGetErrorName(err_), cudaGetErrorString(err_));         \
+            exit(1);                                                                     \
+        }                                                                                \
+    } while (0)
+
+#define MNW_PANIC(...)                                                       \
+    do {                                                                     \
+        fprintf(stderr, "Panic at file %s, line %d:\n", __FILE__, __LINE__); \
+        fprintf(stderr, __VA_ARGS__);                                        \
+        fprintf(stderr, "\n");                                               \
+        exit(1);                                                             \
+    } while (0)
+
+namespace {
+
+// A device buffer that only ever grows (scratch is reused across calls).
+struct Scratch {
+    void *ptr = nullptr;
+    size_t cap = 0;
+    void *need(size_t bytes) {
+        if (bytes > cap) {
+            if (ptr) CUDA_CHECK(cudaFree(ptr));
+            size_t want = bytes + bytes / 4 + 256;
+            CUDA_CHECK(cudaMalloc(&ptr, want));
+            cap = want;
+        }
+        return ptr;
+    }
+    void release() {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace
+
+struct MnwCudaCtx {
+    int device = 0;
+    int64_t launches = 0;
+    uint64_t ditherSeed = 0;
+    Scratch fields, quant, minmax, tileState, tmp, seeds, tableOf, states, misc;
+    Scratch ioA, ioB, ioC;  // host-buffer entry points: device staging
+    uint64_t *jumpPow = nullptr;
+    int *error = nullptr;     // device flag
+    uint32_t *ticket = nullptr;
+    cudaStream_t own = nullptr;  // stream of the synchronous host-buffer entry points
+    cudaStream_t copyIn = nullptr, copyOut = nullptr;
+};
+
+// ---------------------------------------------------------------------------
+// sizes
+// ---------------------------------------------------------------------------
+static inline int64_t nblocks_of(int32_t n) { return ((int64_t)n + kBlockLen - 1) / kBlockLen; }
+
+extern "C" int64_t mnwcuda_FieldFixedBytes(int32_t n) {
+    return (int64_t)sizeof(MnwDiffHeader) + 3 * nblocks_of(n) * (int64_t)sizeof(MnwDiffBlock);
+}
+
+extern "C" int64_t mnwcuda_FieldBound(int32_t n) {
+    int64_t perBlock = ((int64_t)kBlockLen * kMaxWidth / 8 + 15) / 16 * 16;
+    return mnwcuda_FieldFixedBytes(n) + 3 * nblocks_of(n) * perBlock;
+}
+
+// ---------------------------------------------------------------------------
+// dither RNG on the host: only used once per context, to tabulate the jump
+// matrix powers that k_stream_states multiplies with (src/rand.c:80-112).
+// ---------------------------------------------------------------------------
+static inline uint64_t host_next(uint64_t s[2]) {
+    uint64_t a = s[0], b = s[1], sum = a + b;
+    b ^= a;
+    s[0] = ((a << 55) | (a >> 9)) ^ b ^ (b << 14);
+    s[1] = (b << 36) | (b >> 28);
+    return sum;
+}
+
+static void host_jump(uint64_t s[2]) {
+    static const uint64_t poly[2] = {0xbeac0467eba5facbull, 0xd86b048b86aa9922ull};
+    uint64_t a = 0, b = 0;
+    for (int w = 0; w < 2; w++)
+        for (int bit = 0; bit < 64; bit++) {
+            if ((poly[w] >> bit) & 1ull) { a ^= s[0]; b ^= s[1]; }
+            host_next(s);
+        }
+    s[0] = a;
+    s[1] = b;
+}
+
+// columns of J^(2^k), k < kJumpPows; column i = image of basis vector e_i
+static std::vector<uint64_t> jump_powers() {
+    std::vector<uint64_t> m((size_t)kJumpPows * 128 * 2);
+    for (int i = 0; i < 128; i++) {
+        uint64_t s[2] = {i < 64 ? 1ull << i : 0ull, i >= 64 ? 1ull << (i - 64) : 0ull};
+        host_jump(s);
+        m[(size_t)i * 2] = s[0];
+        m[(size_t)i * 2 + 1] = s[1];
+    }
+    for (int k = 1; k < kJumpPows; k++) {
+        const uint64_t *prev = &m[(size_t)(k - 1) * 256];
+        uint64_t *cur = &m[(size_t)k * 256];
+        for (int i = 0; i < 128; i++) {  // cur col i = prev * (prev col i)
+            uint64_t v0 = prev[i * 2], v1 = prev[i * 2 + 1], a = 0, b = 0;
+            for (int j = 0; j < 64; j++) {
+                if ((v0 >> j) & 1ull) { a ^= prev[j * 2]; b ^= prev[j * 2 + 1]; }
+                if ((v1 >> j) & 1ull) { a ^= prev[(64 + j) * 2]; b ^= prev[(64 + j) * 2 + 1]; }
+            }
+            cur[i * 2] = a;
+            cur[i * 2 + 1] = b;
+        }
+    }
+    return m;
+}
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        MNW_PANIC("libminnow_cuda needs a CUDA device and has no CPU fallback (%s).",
+                  cudaGetErrorString(e));
+    if (device < 0) CUDA_CHECK(cudaGetDevice(&device));
+    CUDA_CHECK(cudaSetDevice(device));
+    MnwCudaCtx *ctx = new MnwCudaCtx();
+    ctx->device = device;
+    std::vector<uint64_t> jp = jump_powers();
+    CUDA_CHECK(cudaMalloc(&ctx->jumpPow, jp.size() * sizeof(uint64_t)));
+    CUDA_CHECK(cudaMemcpy(ctx->jumpPow, jp.data(), jp.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    CUDA_CHECK(cudaMalloc(&ctx->error, 256));
+    CUDA_CHECK(cudaMemset(ctx->error, 0, 256));
+    ctx->ticket = reinterpret_cast<uint32_t *>(ctx->error) + 16;
+    CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
+    return ctx;
+}
+
+extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->tmp, &ctx->seeds,
+                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ioA, &ctx->ioB, &ctx->ioC};
+    for (Scratch *s : all) s->release();
+    cudaFree(ctx->jumpPow);
+    cudaFree(ctx->error);
+    cudaStreamDestroy(ctx->own);
+    cudaStreamDestroy(ctx->copyIn);
+    cudaStreamDestroy(ctx->copyOut);
+    delete ctx;
+}
+
+extern "C" int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx) { return ctx->launches; }
+
+extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
+    int err = 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CUDA_CHECK(cudaMemcpyAsync(&err, ctx->error, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    if (err != 0) {
+        CUDA_CHECK(cudaMemsetAsync(ctx->error, 0, sizeof(int), s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+    }
+    return err;
+}
+
+// ---------------------------------------------------------------------------
+// batch plan: host descriptors -> DevField array + totals
+// ---------------------------------------------------------------------------
+namespace {
+
+struct Plan {
+    std::vector<DevField> fields;
+    int64_t nTiles = 0, nBlocks = 0, nTasks = 0, fixedTotal = 0, maxStreams = 0;
+    int uniformTiles = 0, uniformBlocks = 0, uniformTasks = 0;
+};
+
+int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
+    pl.fields.resize((size_t)nFields);
+    bool uniform = true;
+    for (int64_t i = 0; i < nFields; i++) {
+        const MnwFieldDesc &d = h[i];
+        if (d.ParticleLen < 0) return -1;
+        if (d.FieldCode != field_Posn && d.FieldCode != field_Velc) return -3;
+        DevField &f = pl.fields[(size_t)i];
+        f.ioOff = d.Offset;
+        f.fixedBase = pl.fixedTotal;
+        f.firstBlock = pl.nBlocks;
+        f.firstTile = pl.nTiles;
+        f.firstTask = pl.nTasks;
+        f.n = d.ParticleLen;
+        f.nb = (int32_t)nblocks_of(d.ParticleLen);
+        f.fieldCode = d.FieldCode;
+        f.delta = d.Delta;
+        f.width = d.Width;
+        f.tilesPerComp = (f.nb + kTileBlocks - 1) / kTileBlocks;
+        f.seed = d.DitherSeed;
+        int64_t tasks = (3 * (int64_t)f.nb + kRun - 1) / kRun;
+        pl.fixedTotal += mnwcuda_FieldFixedBytes(d.ParticleLen);
+        pl.nBlocks += 3 * (int64_t)f.nb;
+        pl.nTiles += 3 * (int64_t)f.tilesPerComp;
+        pl.nTasks += tasks;
+        if (tasks * 32 > pl.maxStreams) pl.maxStreams = tasks * 32;
+        if (d.ParticleLen != h[0].ParticleLen || d.ParticleLen == 0) uniform = false;
+    }
+    if (uniform && nFields > 0) {
+        pl.uniformTiles = 3 * pl.fields[0].tilesPerComp;
+        pl.uniformBlocks = 3 * pl.fields[0].nb;
+        pl.uniformTasks = (int)((3 * (int64_t)pl.fields[0].nb + kRun - 1) / kRun);
+    }
+    if (pl.nTiles >= (1ll << 31) || pl.nTasks >= (1ll << 31)) return -5;
+    return 0;
+}
+
+EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int64_t outCap,
+                            uint64_t *d_offsets, cudaStream_t s) {
+    const size_t nF = pl.fields.size();
+    EncodeParams p;
+    memset(&p, 0, sizeof(p));
+    p.fields = static_cast<DevField *>(ctx->fields.need(nF * sizeof(DevField)));
+    p.nFields = (int)nF;
+    p.uniformTiles = pl.uniformTiles;
+    p.minmax = static_cast<uint32_t *>(ctx->minmax.need(nF * 6 * sizeof(uint32_t)));
+    p.quant = static_cast<DevQuant *>(ctx->quant.need(nF * sizeof(DevQuant)));
+    p.tileState = static_cast<uint64_t *>(ctx->tileState.need((size_t)(pl.nTiles + 1) * sizeof(uint64_t)));
+    p.ticket = reinterpret_cast<uint32_t *>(p.tileState + pl.nTiles);  // zeroed with the states
+    p.tmp = static_cast<TmpBlock *>(ctx->tmp.need((size_t)(pl.nBlocks + 1) * sizeof(TmpBlock)));
+    p.out = d_out;
+    p.outCap = outCap;
+    p.offsets = d_offsets;
+    p.error = ctx->error;
+    // pageable source: the copy is staged before the call returns
+    CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), nF * sizeof(DevField),
+                               cudaMemcpyHostToDevice, s));
+    CUDA_CHECK(cudaMemsetAsync(p.tileState, 0, (size_t)(pl.nTiles + 1) * sizeof(uint64_t), s));
+    return p;
+}
+
+void launch_pack_and_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParams &p, const uint64_t *qIn,
+                              cudaStream_t s) {
+    const int nF = (int)pl.fields.size();
+    if (pl.nTiles > 0) {
+        if (qIn)
+            k_quantize_delta_pack<true><<<(unsigned)pl.nTiles, 256, 0, s>>>(p, qIn);
+        else
+            k_quantize_delta_pack<false><<<(unsigned)pl.nTiles, 256, 0, s>>>(p, nullptr);
+        ctx->launches++;
+    }
+    int64_t threads = pl.nBlocks > nF + 1 ? pl.nBlocks : nF + 1;
+    k_finalize<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p, pl.nBlocks, pl.nTiles, pl.uniformBlocks);
+    ctx->launches++;
+    CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// device-resident batch encode / decode
+// ---------------------------------------------------------------------------
+extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const MnwFieldDesc *h_fields,
+                                       int64_t nFields, uint8_t *d_out, int64_t outCap,
+                                       uint64_t *d_offsets, void *stream) {
+    if (!ctx || nFields < 0 || nFields >= (1ll << 30)) return -1;
+    if (nFields == 0) return 0;
+    if (((uintptr_t)d_out & 15) || ((uintptr_t)d_in & 3)) return -6;
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Plan pl;
+    int rc = build_plan(h_fields, nFields, pl);
+    if (rc) return rc;
+    EncodeParams p = prepare_encode(ctx, pl, d_out, outCap, d_offsets, s);
+    p.in = d_in;
+    CUDA_CHECK(cudaMemsetAsync(p.minmax, 0xff, (size_t)nFields * 6 * sizeof(uint32_t), s));
+    if (pl.nTiles > 0) {
+        k_unwrap_minmax<<<(unsigned)pl.nTiles, 256, 0, s>>>(p);
+        ctx->launches++;
+    }
+    k_depth<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
+    ctx->launches++;
+    launch_pack_and_finalize(ctx, pl, p, nullptr, s);
+    return 0;
+}
+
+extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, const uint64_t *d_offsets,
+                                       const MnwFieldDesc *h_fields, int64_t nFields, float *d_out,
+                                       void *stream) {
+    if (!ctx || nFields < 0 || nFields >= (1ll << 30)) return -1;
+    if (nFields == 0) return 0;
+    if (((uintptr_t)d_in & 15) || ((uintptr_t)d_out & 3)) return -6;
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Plan pl;
+    int rc = build_plan(h_fields, nFields, pl);
+    if (rc) return rc;
+    const size_t nF = (size_t)nFields;
+    DecodeParams p;
+    memset(&p, 0, sizeof(p));
+    p.in = d_in;
+    p.offsets = d_offsets;
+    p.fields = static_cast<DevField *>(ctx->fields.need(nF * sizeof(DevField)));
+    p.nFields = (int)nF;
+    p.uniformTasks = pl.uniformTasks;
+    p.quant = static_cast<DevQuant *>(ctx->quant.need(nF * sizeof(DevQuant)));
+    p.seeds = static_cast<uint64_t *>(ctx->seeds.need(nF * sizeof(uint64_t)));
+    p.tableOf = static_cast<int *>(ctx->tableOf.need(nF * sizeof(int)));
+    p.maxStreams = pl.maxStreams;
+    p.states = static_cast<uint64_t *>(ctx->states.need(nF * (size_t)pl.maxStreams * 16 + 16));
+    p.jumpPow = ctx->jumpPow;
+    p.out = d_out;
+    p.qOut = nullptr;
+    p.error = ctx->error;
+    CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), nF * sizeof(DevField),
+                               cudaMemcpyHostToDevice, s));
+    k_parse_headers<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
+    ctx->launches++;
+    if (pl.nTasks > 0) {
+        dim3 grid((unsigned)((pl.maxStreams + 127) / 128), (unsigned)nFields);
+        k_stream_states<<<grid, 128, 0, s>>>(p);
+        k_unpack_dequant<false><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
+            p, pl.nTasks);
+        ctx->launches += 2;
+    }
+    CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// host-buffer entry points
+// ---------------------------------------------------------------------------
+namespace {
+
+void accuracy_of(const Field &f, float &delta, float &width) {
+    if (f.Hd.FieldCode == field_Posn) {
+        const PositionAccuracy *a = static_cast<const PositionAccuracy *>(f.Acc);
+        if (!a) MNW_PANIC("Field has no PositionAccuracy.");
+        if (a->Deltas) MNW_PANIC("Per-particle accuracies are not supported by algo_Diff v0.9.");
+        delta = a->Delta;
+        width = a->Width;
+    } else if (f.Hd.FieldCode == field_Velc) {
+        const VelocityAccuracy *a = static_cast<const VelocityAccuracy *>(f.Acc);
+        if (!a) MNW_PANIC("Field has no VelocityAccuracy.");
+        if (a->Deltas) MNW_PANIC("Per-particle accuracies are not supported by algo_Diff v0.9.");
+        if (a->SymLog10Scaled) MNW_PANIC("symLog10 not supported.");  // src/quant.c:749
+        delta = a->Delta;
+        width = 0.0f;
+    } else {
+        MNW_PANIC("Field code %x is not supported by algo_Diff v0.9.", f.Hd.FieldCode);
+    }
+}
+
+void panic_on_status(MnwCudaCtx *ctx, cudaStream_t s, const char *what) {
+    int err = mnwcuda_Status(ctx, s);
+    if (err == kErrDepth)
+        MNW_PANIC("%s: the requested accuracy exceeds the granularity of single precision floats, "
+                  "which only support 24 bits of mantissa precision.", what);  // src/quant.c:688-693
+    if (err == kErrCapacity) MNW_PANIC("%s: output capacity exceeded.", what);
+    if (err == kErrPayload) MNW_PANIC("%s: malformed algo_Diff payload.", what);
+}
+
+void *xmalloc(size_t bytes) {
+    void *p = malloc(bytes ? bytes : 1);
+    if (!p) MNW_PANIC("Allocation failed.");  // AssertAlloc, src/debug.h:36-43
+    return p;
+}
+
+// fetch one field's payload (device region described by two offsets) into malloc memory
+uint8_t *fetch_payload(MnwCudaCtx *ctx, const uint8_t *d_out, const uint64_t *d_off, int64_t *len) {
+    uint64_t off[2];
+    CUDA_CHECK(cudaMemcpyAsync(off, d_off, sizeof(off), cudaMemcpyDeviceToHost, ctx->own));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->own));
+    *len = (int64_t)(off[1] - off[0]);
+    uint8_t *data = static_cast<uint8_t *>(xmalloc((size_t)*len));
+    CUDA_CHECK(cudaMemcpyAsync(data, d_out + off[0], (size_t)*len, cudaMemcpyDeviceToHost, ctx->own));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->own));
+    return data;
+}
+
+}  // namespace
+
+extern "C" void mnwcuda_SetDitherSeed(void *buffer, uint64_t seed) {
+    static_cast<MnwCudaCtx *>(buffer)->ditherSeed = seed;
+}
+
+extern "C" CField mnwcuda_EncodeField(Field f, void *buffer) {
+    MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
+    if (!ctx) MNW_PANIC("mnwcuda_EncodeField needs the buffer returned by MnwCudaCAlloc_v0_9.");
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    MnwFieldDesc d;
+    memset(&d, 0, sizeof(d));
+    d.ParticleLen = f.Hd.ParticleLen;
+    d.FieldCode = f.Hd.FieldCode;
+    d.DitherSeed = ctx->ditherSeed;
+    accuracy_of(f, d.Delta, d.Width);
+    const size_t inBytes = (size_t)d.ParticleLen * 3 * sizeof(float);
+    const int64_t cap = mnwcuda_FieldBound(d.ParticleLen);
+    float *d_in = static_cast<float *>(ctx->ioA.need(inBytes + 16));
+    uint8_t *d_out = static_cast<uint8_t *>(ctx->ioB.need((size_t)cap));
+    uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need(2 * sizeof(uint64_t)));
+    if (inBytes) CUDA_CHECK(cudaMemcpyAsync(d_in, f.Data, inBytes, cudaMemcpyHostToDevice, ctx->own));
+    int rc = mnwcuda_EncodeFieldsDev(ctx, d_in, &d, 1, d_out, cap, d_off, ctx->own);
+    if (rc) MNW_PANIC("mnwcuda_EncodeField: bad field (%d).", rc);
+    panic_on_status(ctx, ctx->own, "mnwcuda_EncodeField");
+    CField cf;
+    memset(&cf, 0, sizeof(cf));
+    cf.Hd = f.Hd;
+    cf.Data = fetch_payload(ctx, d_out, d_off, &cf.DataLen);
+    return cf;
+}
+
+extern "C" Field mnwcuda_DecodeField(CField cf, void *buffer) {
+    MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
+    if (!ctx) MNW_PANIC("mnwcuda_DecodeField needs the buffer returned by MnwCudaDAlloc_v0_9.");
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    if (cf.DataLen < (int64_t)sizeof(MnwDiffHeader)) MNW_PANIC("mnwcuda_DecodeField: payload too short.");
+    MnwDiffHeader h;
+    memcpy(&h, cf.Data, sizeof(h));
+    MnwFieldDesc d;
+    memset(&d, 0, sizeof(d));
+    d.ParticleLen = cf.Hd.ParticleLen;
+    d.FieldCode = cf.Hd.FieldCode;
+    const size_t outBytes = (size_t)d.ParticleLen * 3 * sizeof(float);
+    uint8_t *d_in = static_cast<uint8_t *>(ctx->ioB.need((size_t)cf.DataLen + 16));
+    float *d_out = static_cast<float *>(ctx->ioA.need(outBytes + 16));
+    uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need(2 * sizeof(uint64_t)));
+    uint64_t off[2] = {0, (uint64_t)cf.DataLen};
+    CUDA_CHECK(cudaMemcpyAsync(d_in, cf.Data, (size_t)cf.DataLen, cudaMemcpyHostToDevice, ctx->own));
+    CUDA_CHECK(cudaMemcpyAsync(d_off, off, sizeof(off), cudaMemcpyHostToDevice, ctx->own));
+    int rc = mnwcuda_DecodeFieldsDev(ctx, d_in, d_off, &d, 1, d_out, ctx->own);
+    if (rc) MNW_PANIC("mnwcuda_DecodeField: bad field (%d).", rc);
+    panic_on_status(ctx, ctx->own, "mnwcuda_DecodeField");
+
+    Field f;
+    memset(&f, 0, sizeof(f));
+    f.Hd = cf.Hd;
+    f.Data = xmalloc(outBytes);
+    if (outBytes) CUDA_CHECK(cudaMemcpyAsync(f.Data, d_out, outBytes, cudaMemcpyDeviceToHost, ctx->own));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->own));
+    // reported accuracy: depthToDelta on component 0 (src/quant.c:490-493, 654-662)
+    float delta = (h.X1[0] - h.X0[0]) / (float)(1 << h.Depth);
+    if (cf.Hd.FieldCode == field_Posn) {
+        PositionAccuracy *a = static_cast<PositionAccuracy *>(calloc(1, sizeof(*a)));
+        a->Delta = delta;
+        a->Width = h.Width;
+        f.Acc = a;
+    } else {
+        VelocityAccuracy *a = static_cast<VelocityAccuracy *>(calloc(1, sizeof(*a)));
+        a->Delta = delta;
+        f.Acc = a;
+    }
+    return f;
+}
+
+// Chunks of fields are staged through device buffers one after another;
+// chunk size is bounded so that scratch stays modest.
+extern "C" int64_t mnwcuda_EncodeFieldsHost(MnwCudaCtx *ctx, const float *h_in, const MnwFieldDesc *h_fields,
+                                            int64_t nFields, uint8_t *h_out, int64_t outCap,
+                                            uint64_t *h_offsets) {
+    if (!ctx || nFields < 0) return -1;
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    const int64_t kChunkFloats = 192ll << 20;  // 768 MiB of input per chunk
+    int64_t total = 0, i = 0;
+    h_offsets[0] = 0;
+    std::vector<MnwFieldDesc> local;
+    std::vector<uint64_t> offs;
+    while (i < nFields) {
+        local.clear();
+        int64_t floats = 0, bound = 0, j = i;
+        while (j < nFields && (j == i || floats + 3ll * h_fields[j].ParticleLen <= kChunkFloats)) {
+            MnwFieldDesc d = h_fields[j];
+            d.Offset = floats;
+            floats += 3ll * d.ParticleLen;
+            bound += mnwcuda_FieldBound(d.ParticleLen);
+            local.push_back(d);
+            j++;
+        }
+        const int64_t cnt = j - i;
+        float *d_in = static_cast<float *>(ctx->ioA.need((size_t)floats * 4 + 16));
+        uint8_t *d_out = static_cast<uint8_t *>(ctx->ioB.need((size_t)bound));
+        uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need((size_t)(cnt + 1) * 8));
+        for (int64_t k = 0; k < cnt; k++) {
+            size_t bytes = (size_t)local[(size_t)k].ParticleLen * 12;
+            if (bytes)
+                CUDA_CHECK(cudaMemcpyAsync(d_in + local[(size_t)k].Offset, h_in + h_fields[i + k].Offset, bytes,
+                                           cudaMemcpyHostToDevice, ctx->own));
+        }
+        int rc = mnwcuda_EncodeFieldsDev(ctx, d_in, local.data(), cnt, d_out, bound, d_off, ctx->own);
+        if (rc) return rc;
+        offs.resize((size_t)cnt + 1);
+        CUDA_CHECK(cudaMemcpyAsync(offs.data(), d_off, (size_t)(cnt + 1) * 8, cudaMemcpyDeviceToHost, ctx->own));
+        int err = mnwcuda_Status(ctx, ctx->own);
+        if (err) return -100 - err;
+        const int64_t bytes = (int64_t)offs[(size_t)cnt];
+        if (total + bytes > outCap) return -2;
+        CUDA_CHECK(cudaMemcpyAsync(h_out + total, d_out, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->own));
+        CUDA_CHECK(cudaStreamSynchronize(ctx->own));
+        for (int64_t k = 0; k <= cnt; k++) h_offsets[i + k] = (uint64_t)total + offs[(size_t)k];
+        total += bytes;
+        i = j;
+    }
+    return total;
+}
+
+extern "C" int mnwcuda_DecodeFieldsHost(MnwCudaCtx *ctx, const uint8_t *h_in, const uint64_t *h_offsets,
+                                        const MnwFieldDesc *h_fields, int64_t nFields, float *h_out) {
+    if (!ctx || nFields < 0) return -1;
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    const int64_t kChunkFloats = 192ll << 20;
+    int64_t i = 0;
+    std::vector<MnwFieldDesc> local;
+    std::vector<uint64_t> offs;
+    while (i < nFields) {
+        local.clear();
+        int64_t floats = 0, j = i;
+        while (j < nFields && (j == i || floats + 3ll * h_fields[j].ParticleLen <= kChunkFloats)) {
+            MnwFieldDesc d = h_fields[j];
+            d.Offset = floats;
+            floats += 3ll * d.ParticleLen;
+            local.push_back(d);
+            j++;
+        }
+        const int64_t cnt = j - i;
+        const uint64_t base = h_offsets[i];
+        if (base & 15) return -6;
+        const int64_t bytes = (int64_t)(h_offsets[j] - base);
+        offs.resize((size_t)cnt + 1);
+        for (int64_t k = 0; k <= cnt; k++) offs[(size_t)k] = h_offsets[i + k] - base;
+        uint8_t *d_in = static_cast<uint8_t *>(ctx->ioB.need((size_t)bytes + 16));
+        float *d_out = static_cast<float *>(ctx->ioA.need((size_t)floats * 4 + 16));
+        uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need((size_t)(cnt + 1) * 8));
+        CUDA_CHECK(cudaMemcpyAsync(d_in, h_in + base, (size_t)bytes, cudaMemcpyHostToDevice, ctx->own));
+        CUDA_CHECK(cudaMemcpyAsync(d_off, offs.data(), (size_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, ctx->own));
+        int rc = mnwcuda_DecodeFieldsDev(ctx, d_in, d_off, local.data(), cnt, d_out, ctx->own);
+        if (rc) return rc;
+        for (int64_t k = 0; k < cnt; k++) {
+            size_t nb = (size_t)local[(size_t)k].ParticleLen * 12;
+            if (nb)
+                CUDA_CHECK(cudaMemcpyAsync(h_out + h_fields[i + k].Offset, d_out + local[(size_t)k].Offset, nb,
+                                           cudaMemcpyDeviceToHost, ctx->own));
+        }
+        int err = mnwcuda_Status(ctx, ctx->own);
+        if (err) return -100 - err;
+        i = j;
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// the six plugin functions (src/register.h:15-22): literal QField <-> CField
+// ---------------------------------------------------------------------------
+extern "C" void *MnwCudaCAlloc_v0_9(void) { return mnwcuda_Create(-1); }
+extern "C" void MnwCudaCFree_v0_9(void *buffer) { mnwcuda_Destroy(static_cast<MnwCudaCtx *>(buffer)); }
+extern "C" void *MnwCudaDAlloc_v0_9(void) { return mnwcuda_Create(-1); }
+extern "C" void MnwCudaDFree_v0_9(void *buffer) { mnwcuda_Destroy(static_cast<MnwCudaCtx *>(buffer)); }
+
+extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
+    MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
+    if (!ctx) MNW_PANIC("MnwCudaCompress_v0_9 needs the buffer returned by MnwCudaCAlloc_v0_9.");
+    if (!qf.Quant) MNW_PANIC("QField.Quant is NULL: the quantizer must attach its Quantization.");
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->own;
+    MnwFieldDesc d;
+    memset(&d, 0, sizeof(d));
+    d.ParticleLen = qf.Hd.ParticleLen;
+    d.FieldCode = qf.Hd.FieldCode;
+    d.DitherSeed = ctx->ditherSeed;
+    DevQuant dq;
+    memset(&dq, 0, sizeof(dq));
+    if (qf.Hd.FieldCode == field_Posn) {
+        const PositionQuantization *q = static_cast<const PositionQuantization *>(qf.Quant);
+        if (q->Depths) MNW_PANIC("Per-particle depths are not supported by algo_Diff v0.9.");
+        d.Width = q->Width;
+        for (int c = 0; c < 3; c++) { dq.X0[c] = q->X0[c]; dq.X1[c] = q->X1[c]; }
+        dq.depth = q->Depth;
+    } else if (qf.Hd.FieldCode == field_Velc) {
+        const VelocityQuantization *q = static_cast<const VelocityQuantization *>(qf.Quant);
+        if (q->Depths) MNW_PANIC("Per-particle depths are not supported by algo_Diff v0.9.");
+        if (q->SymLog10Scaled) MNW_PANIC("symLog10 not supported.");
+        for (int c = 0; c < 3; c++) { dq.X0[c] = q->X0[c]; dq.X1[c] = q->X1[c]; }
+        dq.depth = q->Depth;
+    } else {
+        MNW_PANIC("Field code %x is not supported by algo_Diff v0.9.", qf.Hd.FieldCode);
+    }
+    if (dq.depth > 24) MNW_PANIC("Quantization depth %u exceeds 24.", dq.depth);
+    for (int c = 0; c < 3; c++)
+        if (dq.maxDiff < dq.X1[c] - dq.X0[c]) dq.maxDiff = dq.X1[c] - dq.X0[c];
+
+    Plan pl;
+    if (build_plan(&d, 1, pl)) MNW_PANIC("MnwCudaCompress_v0_9: bad field.");
+    const size_t inBytes = (size_t)d.ParticleLen * 3 * sizeof(uint64_t);
+    const int64_t cap = mnwcuda_FieldBound(d.ParticleLen);
+    uint64_t *d_q = static_cast<uint64_t *>(ctx->ioA.need(inBytes + 16));
+    uint8_t *d_out = static_cast<uint8_t *>(ctx->ioB.need((size_t)cap));
+    uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need(2 * sizeof(uint64_t)));
+    if (inBytes) CUDA_CHECK(cudaMemcpyAsync(d_q, qf.Data, inBytes, cudaMemcpyHostToDevice, s));
+    EncodeParams p = prepare_encode(ctx, pl, d_out, cap, d_off, s);
+    CUDA_CHECK(cudaMemcpyAsync(p.quant, &dq, sizeof(dq), cudaMemcpyHostToDevice, s));
+    launch_pack_and_finalize(ctx, pl, p, d_q, s);
+    panic_on_status(ctx, s, "MnwCudaCompress_v0_9");
+    CField cf;
+    memset(&cf, 0, sizeof(cf));
+    cf.Hd = qf.Hd;
+    cf.Data = fetch_payload(ctx, d_out, d_off, &cf.DataLen);
+    return cf;
+}
+
+extern "C" QField MnwCudaDecompress_v0_9(CField cf, void *buffer) {
+    MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
+    if (!ctx) MNW_PANIC("MnwCudaDecompress_v0_9 needs the buffer returned by MnwCudaDAlloc_v0_9.");
+    if (cf.DataLen < (int64_t)sizeof(MnwDiffHeader)) MNW_PANIC("MnwCudaDecompress_v0_9: payload too short.");
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->own;
+    MnwDiffHeader h;
+    memcpy(&h, cf.Data, sizeof(h));
+    MnwFieldDesc d;
+    memset(&d, 0, sizeof(d));
+    d.ParticleLen = cf.Hd.ParticleLen;
+    d.FieldCode = cf.Hd.FieldCode;
+    Plan pl;
+    if (build_plan(&d, 1, pl)) MNW_PANIC("MnwCudaDecompress_v0_9: bad field.");
+    const size_t outBytes = (size_t)d.ParticleLen * 3 * sizeof(uint64_t);
+    uint8_t *d_in = static_cast<uint8_t *>(ctx->ioB.need((size_t)cf.DataLen + 16));
+    uint64_t *d_q = static_cast<uint64_t *>(ctx->ioA.need(outBytes + 16));
+    uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need(2 * sizeof(uint64_t)));
+    uint64_t off[2] = {0, (uint64_t)cf.DataLen};
+    CUDA_CHECK(cudaMemcpyAsync(d_in, cf.Data, (size_t)cf.DataLen, cudaMemcpyHostToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(d_off, off, sizeof(off), cudaMemcpyHostToDevice, s));
+    DecodeParams p;
+    memset(&p, 0, sizeof(p));
+    p.in = d_in;
+    p.offsets = d_off;
+    p.fields = static_cast<DevField *>(ctx->fields.need(sizeof(DevField)));
+    p.nFields = 1;
+    p.uniformTasks = pl.uniformTasks;
+    p.quant = static_cast<DevQuant *>(ctx->quant.need(sizeof(DevQuant)));
+    p.seeds = static_cast<uint64_t *>(ctx->seeds.need(sizeof(uint64_t)));
+    p.tableOf = static_cast<int *>(ctx->tableOf.need(sizeof(int)));
+    p.maxStreams = pl.maxStreams;
+    p.jumpPow = ctx->jumpPow;
+    p.qOut = d_q;
+    p.error = ctx->error;
+    CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), sizeof(DevField),
+                               cudaMemcpyHostToDevice, s));
+    k_parse_headers<<<1, 128, 0, s>>>(p);
+    ctx->launches++;
+    if (pl.nTasks > 0) {
+        k_unpack_dequant<true><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
+            p, pl.nTasks);
+        ctx->launches++;
+    }
+    CUDA_CHECK(cudaGetLastError());
+    panic_on_status(ctx, s, "MnwCudaDecompress_v0_9");
+
+    QField qf;
+    memset(&qf, 0, sizeof(qf));
+    qf.Hd = cf.Hd;
+    qf.Data = static_cast<uint64_t *>(xmalloc(outBytes));
+    if (outBytes) CUDA_CHECK(cudaMemcpyAsync(qf.Data, d_q, outBytes, cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    if (cf.Hd.FieldCode == field_Posn) {
+        PositionQuantization *q = static_cast<PositionQuantization *>(calloc(1, sizeof(*q)));
+        q->Width = h.Width;
+        for (int c = 0; c < 3; c++) { q->X0[c] = h.X0[c]; q->X1[c] = h.X1[c]; }
+        q->Depth = h.Depth;
+        qf.Quant = q;
+    } else {
+        VelocityQuantization *q = static_cast<VelocityQuantization *>(calloc(1, sizeof(*q)));
+        for (int c = 0; c < 3; c++) { q->X0[c] = h.X0[c]; q->X1[c] = h.X1[c]; }
+        q->Depth = h.Depth;
+        qf.Quant = q;
+    }
+    return qf;
+}
+
+// ---------------------------------------------------------------------------
+// synthetic input
+// ---------------------------------------------------------------------------
+static inline uint64_t host_splitmix(uint64_t &s) {
+    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+extern "C" int mnwcuda_GenerateZeldovich(MnwCudaCtx *ctx, int32_t ngrid, float boxWidth, uint64_t seed,
+                                         int64_t firstId, int64_t count, float *d_pos, float *d_vel,
+                                         void *stream) {
+    if (!ctx || ngrid <= 0 || count < 0) return -1;
+    if (count == 0) return 0;
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    // 64 integer wave-vectors with |k_i| <= 8, amplitude ~ |k|^-2 along k,
+    // rescaled to an rms displacement of 1.5 cells; velocity = 200 * (psi in cells)
+    GenModes m;
+    uint64_t s = seed;
+    double sumsq = 0.0;
+    double ax[kGenModes], ay[kGenModes], az[kGenModes];
+    for (int i = 0; i < kGenModes; i++) {
+        int kx, ky, kz;
+        do {
+            kx = (int)(host_splitmix(s) % 17) - 8;
+            ky = (int)(host_splitmix(s) % 17) - 8;
+            kz = (int)(host_splitmix(s) % 17) - 8;
+        } while (kx == 0 && ky == 0 && kz == 0);
+        double k2 = (double)kx * kx + (double)ky * ky + (double)kz * kz;
+        double a = 1.0 / k2, inv = 1.0 / sqrt(k2);
+        m.kx[i] = kx; m.ky[i] = ky; m.kz[i] = kz;
+        m.phase[i] = (float)((double)(host_splitmix(s) >> 11) * (1.0 / 9007199254740992.0) * 6.283185307179586);
+        ax[i] = a * kx * inv; ay[i] = a * ky * inv; az[i] = a * kz * inv;
+        sumsq += a * a;
+    }
+    const double cell = (double)boxWidth / ngrid;
+    const double scale = 1.5 * cell / sqrt(sumsq / 2.0);
+    for (int i = 0; i < kGenModes; i++) {
+        m.ax[i] = (float)(ax[i] * scale); m.ay[i] = (float)(ay[i] * scale); m.az[i] = (float)(az[i] * scale);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CUDA_CHECK(cudaMemcpyToSymbolAsync(cModes, &m, sizeof(m), 0, cudaMemcpyHostToDevice, st));
+    GenParams p;
+    p.ngrid = ngrid;
+    p.L = boxWidth;
+    p.velPerLen = (float)(200.0 / cell);
+    p.firstId = firstId;
+    p.count = count;
+    p.pos = d_pos;
+    p.vel = d_vel;
+    k_zeldovich<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(p);
+    ctx->launches++;
+    CUDA_CHECK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,136 @@
+// minnow_kernels.cuh -- device structs and helpers shared by the kernels of
+// libminnow_cuda (sm_100a only). No CPU fallback lives anywhere in this tree.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "minnow_cuda.h"
+
+namespace mnw {
+
+constexpr int kBlockLen = MNWCUDA_BLOCK_LEN;   // values per pack block (one warp)
+constexpr int kChunk = 32;                     // consecutive values per lane
+constexpr int kWarpsPerCta = 8;                // encode: one block per warp
+constexpr int kTileBlocks = kWarpsPerCta;      // blocks per encode tile
+constexpr int kTileVals = kTileBlocks * kBlockLen;
+constexpr int kRun = MNWCUDA_DITHER_RUN;       // blocks per decode task
+constexpr int kMaxWidth = 25;                  // residual bits: |delta| < 2^24
+constexpr int kStageWords = 1024;              // per-warp staging, 4 KiB
+
+enum : int { kErrDepth = 1, kErrCapacity = 2, kErrPayload = 3 };
+
+// One field of the batch as the kernels see it (built on the host per call).
+struct DevField {
+    int64_t ioOff;       // first float of the field in the float buffer
+    int64_t fixedBase;   // sum of fixed bytes (header+table) of earlier fields
+    int64_t firstBlock;  // sum of 3*nb of earlier fields
+    int64_t firstTile;   // encode tiles of earlier fields
+    int64_t firstTask;   // decode tasks of earlier fields
+    int32_t n;           // particles
+    int32_t nb;          // blocks per component
+    uint32_t fieldCode;
+    float delta;
+    float width;
+    int32_t tilesPerComp;
+    uint64_t seed;
+};
+
+// Quantisation parameters of one field (PositionQuantization, types.h:82-87).
+struct DevQuant {
+    float X0[3];
+    float X1[3];
+    float maxDiff;
+    uint32_t depth;
+};
+
+// Per-block result of the pack kernel before the table is finalised.
+struct TmpBlock {
+    uint32_t first;
+    int32_t minDelta;
+    uint32_t width;
+    uint32_t pad;
+    uint64_t prefix16;  // payload offset over the whole batch, 16-byte units
+};
+
+// ---- order-preserving float <-> uint32 (for atomicMin/atomicMax) ----
+__device__ __forceinline__ uint32_t ord_from_float(float v) {
+    uint32_t b = __float_as_uint(v);
+    return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float float_from_ord(uint32_t o) {
+    uint32_t b = o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu);
+    return __uint_as_float(b);
+}
+
+// util_UndoPeriodic's per-element rule (src/util.c:106-110)
+__device__ __forceinline__ float unwrap(float v, float anchor, float L, float half) {
+    float rel = __fsub_rn(v, anchor);
+    if (rel >= half) return __fsub_rn(v, L);
+    if (rel < -half) return __fadd_rn(v, L);
+    return v;
+}
+
+// util_Periodic's per-element rule (src/util.c:76-82)
+__device__ __forceinline__ float wrap(float v, float L) {
+    if (v >= L) return __fsub_rn(v, L);
+    if (v < 0.0f) return __fadd_rn(v, L);
+    return v;
+}
+
+// util_UniformBinIndex's per-element rule (src/util.c:184-191): IEEE division,
+// clamp, scale, truncate. No contraction anywhere.
+__device__ __forceinline__ uint32_t bin_index(float v, float x0, float dx, float bins,
+                                              uint32_t top) {
+    float t = __fdiv_rn(__fsub_rn(v, x0), dx);
+    if (t < 0.0f) return 0u;
+    if (t >= 1.0f) return top;
+    return __float2uint_rz(__fmul_rn(t, bins));
+}
+
+// xorshift128+ (55,14,36), src/rand.c:80-90; returns s0+s1 of the old state
+__device__ __forceinline__ uint64_t xs128p_next(uint64_t &s0, uint64_t &s1) {
+    uint64_t a = s0, b = s1;
+    uint64_t sum = a + b;
+    b ^= a;
+    s0 = ((a << 55) | (a >> 9)) ^ b ^ (b << 14);
+    s1 = (b << 36) | (b >> 28);
+    return sum;
+}
+
+// staging layout for packed words: one pad word after every 32, so that lanes
+// walking rows of `w` words and lanes walking consecutive words both spread
+// over the banks
+__device__ __forceinline__ int skew(int m) { return m + (m >> 5); }
+
+// staging layout for 32x32 float transposes: 16-byte chunk j of row r sits at
+// chunk position j ^ (r & 7) (the 128-byte XOR swizzle)
+__device__ __forceinline__ int swz_chunk(int row, int j) { return row * 8 + (j ^ (row & 7)); }
+
+// tile/task -> field lookup: largest f with first[f] <= idx
+template <typename GetFirst>
+__device__ __forceinline__ int find_field(int nFields, int64_t idx, GetFirst first) {
+    int lo = 0, hi = nFields - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (first(mid) <= idx) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(uint64_t *p, uint64_t v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ float4 ld_stream_f4(const float4 *p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+}  // namespace mnw
