@@ -102,6 +102,12 @@ int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in,
 int mnwcuda_Status(MnwCudaCtx *ctx, void *stream);
 /* Kernels launched by this context since creation (bench bookkeeping). */
 int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx);
+/* Per-kernel device times of the most recent Encode/DecodeFieldsDev call
+ * (bench bookkeeping; CUDA events on the call's stream, off by default).
+ * ms[0..3] = unwrap_minmax, depth, quantize_delta_pack, finalize;
+ * ms[4..6] = parse_headers, stream_states, unpack_dequant; -1 = not run. */
+void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on);
+int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms /* [7] */);
 
 /* ---- host-buffer entry points (reference-facing, synchronous) ----
  * mnwcuda_EncodeField == CFunc(quant_QField(f)); the returned CField.Data is

@@ -102,6 +102,8 @@ EXPORTS = {
                                           C.c_void_p, C.c_void_p]),
     "mnwcuda_Status": (C.c_int, [C.c_void_p, C.c_void_p]),
     "mnwcuda_LaunchCount": (C.c_int64, [C.c_void_p]),
+    "mnwcuda_EnableKernelTiming": (None, [C.c_void_p, C.c_int]),
+    "mnwcuda_KernelTimes": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "mnwcuda_EncodeField": (CField, [Field, C.c_void_p]),
     "mnwcuda_DecodeField": (Field, [CField, C.c_void_p]),
     "mnwcuda_EncodeFieldsHost": (C.c_int64, [C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64, C.c_void_p,
@@ -192,6 +194,19 @@ class Codec:
     @property
     def launches(self):
         return lib().mnwcuda_LaunchCount(self.ctx)
+
+    KERNEL_NAMES = ("k_unwrap_minmax", "k_depth", "k_quantize_delta_pack", "k_finalize",
+                    "k_parse_headers", "k_stream_states", "k_unpack_dequant")
+
+    def enable_kernel_timing(self, on=True):
+        lib().mnwcuda_EnableKernelTiming(self.ctx, 1 if on else 0)
+
+    def kernel_times(self):
+        """ms per kernel of the most recent encode_dev / decode_dev (waits for them)."""
+        ms = (C.c_float * 7)()
+        if lib().mnwcuda_KernelTimes(self.ctx, ms):
+            raise RuntimeError("kernel timing is not enabled")
+        return dict(zip(self.KERNEL_NAMES, [float(v) for v in ms]))
 
     # ---- device-resident batch path ----
     def encode_dev(self, d_in, descs, n_fields, d_out, d_offsets, stream=None):

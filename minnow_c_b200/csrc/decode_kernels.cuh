@@ -55,6 +55,7 @@ __global__ void k_parse_headers(DecodeParams p) {
     }
     q.maxDiff = md;
     q.depth = ok ? h.Depth : 0xffffffffu;
+    q.width = h.Width;
     p.quant[f] = q;
     p.seeds[f] = h.DitherSeed;
     const MnwDiffHeader *h0 = reinterpret_cast<const MnwDiffHeader *>(p.in + p.offsets[0]);
@@ -157,7 +158,7 @@ __global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams 
         s1 = sp[1];
     }
     const bool isPos = fd.fieldCode == field_Posn;
-    const float L = fd.width;
+    const float L = qp.width;  // the encoder's box width, not the caller's
     const float bw = __fdiv_rn(qp.maxDiff, (float)(1u << qp.depth));
 
     const int gEnd = min(3 * fd.nb, (localTask + 1) * kRun);

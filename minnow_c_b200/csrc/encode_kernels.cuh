@@ -130,6 +130,7 @@ __global__ void k_depth(EncodeParams p) {
         depth = 24;
     }
     q.depth = (uint32_t)depth;
+    q.width = fd.width;
     p.quant[f] = q;
 }
 

@@ -72,7 +72,16 @@ struct MnwCudaCtx {
     uint32_t *ticket = nullptr;
     cudaStream_t own = nullptr;  // stream of the synchronous host-buffer entry points
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
+    bool timing = false;         // mnwcuda_EnableKernelTiming
+    cudaEvent_t ev[10] = {};     // encode: 0..4, decode: 5..8
+    bool evSet[10] = {};
 };
+
+static inline void mark(MnwCudaCtx *ctx, int i, cudaStream_t s) {
+    if (!ctx->timing) return;
+    CUDA_CHECK(cudaEventRecord(ctx->ev[i], s));
+    ctx->evSet[i] = true;
+}
 
 // ---------------------------------------------------------------------------
 // sizes
@@ -174,10 +183,37 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaStreamDestroy(ctx->own);
     cudaStreamDestroy(ctx->copyIn);
     cudaStreamDestroy(ctx->copyOut);
+    for (cudaEvent_t e : ctx->ev)
+        if (e) cudaEventDestroy(e);
     delete ctx;
 }
 
 extern "C" int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx) { return ctx->launches; }
+
+extern "C" void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on) {
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    ctx->timing = on != 0;
+    if (ctx->timing)
+        for (cudaEvent_t &e : ctx->ev)
+            if (!e) CUDA_CHECK(cudaEventCreate(&e));
+}
+
+// ms[0..3] = K1 unwrap_minmax, K1b depth, K2 quantize_delta_pack, K2f finalize
+// ms[4..6] = K3p parse_headers, K3a stream_states, K3 unpack_dequant
+extern "C" int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms) {
+    if (!ctx->timing) return -1;
+    CUDA_CHECK(cudaSetDevice(ctx->device));
+    static const int first[7] = {0, 1, 2, 3, 5, 6, 7};
+    for (int k = 0; k < 7; k++) {
+        int a = first[k], b = a + 1;
+        ms[k] = -1.0f;
+        if (ctx->evSet[a] && ctx->evSet[b]) {
+            CUDA_CHECK(cudaEventSynchronize(ctx->ev[b]));
+            CUDA_CHECK(cudaEventElapsedTime(&ms[k], ctx->ev[a], ctx->ev[b]));
+        }
+    }
+    return 0;
+}
 
 extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
     int err = 0;
@@ -273,9 +309,11 @@ void launch_pack_and_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParam
             k_quantize_delta_pack<false><<<(unsigned)pl.nTiles, 256, 0, s>>>(p, nullptr);
         ctx->launches++;
     }
+    mark(ctx, 3, s);
     int64_t threads = pl.nBlocks > nF + 1 ? pl.nBlocks : nF + 1;
     k_finalize<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p, pl.nBlocks, pl.nTiles, pl.uniformBlocks);
     ctx->launches++;
+    mark(ctx, 4, s);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -298,12 +336,15 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     EncodeParams p = prepare_encode(ctx, pl, d_out, outCap, d_offsets, s);
     p.in = d_in;
     CUDA_CHECK(cudaMemsetAsync(p.minmax, 0xff, (size_t)nFields * 6 * sizeof(uint32_t), s));
+    mark(ctx, 0, s);
     if (pl.nTiles > 0) {
         k_unwrap_minmax<<<(unsigned)pl.nTiles, 256, 0, s>>>(p);
         ctx->launches++;
     }
+    mark(ctx, 1, s);
     k_depth<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
     ctx->launches++;
+    mark(ctx, 2, s);
     launch_pack_and_finalize(ctx, pl, p, nullptr, s);
     return 0;
 }
@@ -338,13 +379,17 @@ extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, con
     p.error = ctx->error;
     CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), nF * sizeof(DevField),
                                cudaMemcpyHostToDevice, s));
+    mark(ctx, 5, s);
     k_parse_headers<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
     ctx->launches++;
+    mark(ctx, 6, s);
     if (pl.nTasks > 0) {
         dim3 grid((unsigned)((pl.maxStreams + 127) / 128), (unsigned)nFields);
         k_stream_states<<<grid, 128, 0, s>>>(p);
+        mark(ctx, 7, s);
         k_unpack_dequant<false><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
             p, pl.nTasks);
+        mark(ctx, 8, s);
         ctx->launches += 2;
     }
     CUDA_CHECK(cudaGetLastError());

@@ -42,6 +42,7 @@ struct DevQuant {
     float X1[3];
     float maxDiff;
     uint32_t depth;
+    float width;  // decode: box width from the payload header (Posn)
 };
 
 // Per-block result of the pack kernel before the table is finalised.
