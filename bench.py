@@ -303,6 +303,10 @@ def run_b200(args):
             base = torch.cumsum(sizes, 0)[rank] - sizes[rank]  # noqa: F841
         if record:
             record[1].record()
+        if args.encode_only:
+            if record:
+                record[2].record()
+            return
         codec.decode_dev(d_out, d_off, descs, nf, d_dec)
         if record:
             record[2].record()
@@ -310,7 +314,7 @@ def run_b200(args):
     for _ in range(max(args.warmup, 1)):
         step()
     torch.cuda.synchronize()
-    if codec.status() != 0:
+    if codec.status() != 0 and not args.encode_only:
         raise SystemExit("device-side error during warm-up")
     comp_bytes = int(d_off[nf].item())
 
@@ -338,8 +342,14 @@ def run_b200(args):
     clk = clocks.stop() if rank == 0 else None
     launches = codec.launches - launches0
     codec.enable_kernel_timing(False)
-    if codec.status() != 0:
+    if codec.status() != 0 and not args.encode_only:
         raise SystemExit("device-side error during the timed region")
+    if args.encode_only:
+        if rank == 0:
+            em = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+            print(json.dumps({"encode_only_ms": em, "debug_mask": os.environ.get("MNWCUDA_DEBUG_MASK")}), flush=True)
+        codec.close()
+        return 0
 
     enc_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
     dec_ms = sum(e[1].elapsed_time(e[2]) for e in evs)
@@ -353,7 +363,7 @@ def run_b200(args):
     check = roundtrip_check(torch, d_in, d_dec, fields, seg)
 
     # ---- e2e through the host-buffer C ABI (pinned host memory) ----
-    e2e = run_e2e(torch, mc, codec, d_in, args, n_gpus, dev, world)
+    e2e = None if args.no_e2e else run_e2e(torch, mc, codec, d_in, args, n_gpus, dev, world)
 
     value = n_gpus * 2 * raw_bytes * args.steps / (tot_ms * 1e-3) / 1e9
     enc_gbs = n_gpus * raw_bytes * args.steps / (enc_ms * 1e-3) / 1e9
@@ -369,11 +379,10 @@ def run_b200(args):
     kt = ktimes[-1]
     c = comp_bytes / (nf * 3 * seg)  # compressed bytes per value (payload + tables + headers)
     alg_bytes = (4.0 + c) * nf * 3 * seg  # per launch: SURVEY 8(d): encode 4 B read + c B written; decode mirror
-    dom = "k_quantize_delta_pack" if kt["k_quantize_delta_pack"] >= kt["k_unpack_dequant"] else "k_unpack_dequant"
+    dom = "k_encode" if kt["k_encode"] >= kt["k_unpack_dequant"] else "k_unpack_dequant"
     roof = {}
-    for name in ("k_quantize_delta_pack", "k_unpack_dequant", "k_unwrap_minmax"):
-        b = alg_bytes if name != "k_unwrap_minmax" else 4.0 * nf * 3 * seg
-        roof[name] = {"ms": kt[name], "achieved": b / (kt[name] * 1e-3) / 1e9, "alg_bytes": b}
+    for name in ("k_encode", "k_unpack_dequant"):
+        roof[name] = {"ms": kt[name], "achieved": alg_bytes / (kt[name] * 1e-3) / 1e9, "alg_bytes": alg_bytes}
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": roof[dom]["achieved"], "peak": peak, "unit": "GB/s",
         "frac": roof[dom]["achieved"] / peak, "traffic": load_traffic(dom), "peak_source": peak_src,
@@ -522,6 +531,8 @@ def main():
     ap.add_argument("--segments", type=int, default=256, help="segments of 2^22 particles per GPU")
     ap.add_argument("--e2e-segments", type=int, default=32)
     ap.add_argument("--cpu-segments", type=int, default=0, help="CPU arm sample (0 = from the core count)")
+    ap.add_argument("--encode-only", action="store_true", help="kernel experiments: time encode only, no checks")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer e2e leg (kernel experiments)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.steps < 1:

@@ -98,14 +98,16 @@ int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in,
                             float *d_out, void *stream);
 /* Waits for `stream` and returns 0 or the first device-side error of the
  * calls since the last Status: 1 = accuracy needs depth > 24 (the Panic of
- * src/quant.c:688-693), 2 = output capacity exceeded, 3 = malformed payload. */
+ * src/quant.c:688-693), 2 = output capacity exceeded, 3 = malformed payload,
+ * 4 = quantised integers at the CFunc boundary exceed 24 bits. */
 int mnwcuda_Status(MnwCudaCtx *ctx, void *stream);
 /* Kernels launched by this context since creation (bench bookkeeping). */
 int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx);
 /* Per-kernel device times of the most recent Encode/DecodeFieldsDev call
  * (bench bookkeeping; CUDA events on the call's stream, off by default).
- * ms[0..3] = unwrap_minmax, depth, quantize_delta_pack, finalize;
- * ms[4..6] = parse_headers, stream_states, unpack_dequant; -1 = not run. */
+ * ms[0] = k_encode (min/max + quantise + delta + pack, fused), ms[1] =
+ * k_finalize, ms[2..3] unused; ms[4..6] = k_parse_headers, k_stream_states,
+ * k_unpack_dequant; -1 = not run. */
 void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on);
 int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms /* [7] */);
 

@@ -195,7 +195,7 @@ class Codec:
     def launches(self):
         return lib().mnwcuda_LaunchCount(self.ctx)
 
-    KERNEL_NAMES = ("k_unwrap_minmax", "k_depth", "k_quantize_delta_pack", "k_finalize",
+    KERNEL_NAMES = ("k_encode", "k_finalize", "_unused2", "_unused3",
                     "k_parse_headers", "k_stream_states", "k_unpack_dequant")
 
     def enable_kernel_timing(self, on=True):

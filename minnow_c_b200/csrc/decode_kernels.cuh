@@ -5,6 +5,7 @@
 // util_UndoUniformBinIndex (src/util.c:223-242) and the RNG of src/rand.c.
 #pragma once
 
+#include "bitpack.cuh"
 #include "minnow_kernels.cuh"
 
 namespace mnw {
@@ -113,9 +114,13 @@ __global__ void __launch_bounds__(128) k_stream_states(DecodeParams p) {
 // ---------------------------------------------------------------------------
 // K3: one warp per dither task = 32 consecutive blocks of one field; lane l
 // owns stream task*32+l and values [32l, 32l+32) of every block it visits.
-//   unpack  util_U32UndoUniformPack (src/util.c:383-403): coalesced word
-//           loads staged through skewed shared memory, lane reads its `width`
-//           words and shifts its 32 residuals out
+// There is no CTA-wide synchronisation: warps are independent and latency is
+// hidden by occupancy.
+//   table   lane i holds the table entry of the task's block i (one coalesced
+//           512-byte load), broadcast by shuffle when the block is visited
+//   unpack  util_U32UndoUniformPack (src/util.c:383-403): 128-bit coalesced
+//           loads staged through skewed shared memory, width-specialised
+//           extraction of the lane's 32 residuals from its `width` words
 //   scan    q[j] = first + sum_{i<=j} (r[i]+minDelta): lane-local inclusive
 //           sums + warp shuffle scan of the lane totals
 //   dequant util_UndoUniformBinIndex (src/util.c:229-238), two separately
@@ -125,8 +130,33 @@ __global__ void __launch_bounds__(128) k_stream_states(DecodeParams p) {
 // ---------------------------------------------------------------------------
 constexpr int kDecWarps = 4;
 
+template <bool kGuard>
+__device__ __forceinline__ void dequant_block(const uint32_t (&r)[kChunk], uint32_t base, float x0, float bw,
+                                              bool isPos, float L, int lane, int len, uint64_t &s0,
+                                              uint64_t &s1, float *sf) {
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        float o[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int idx = j * 4 + i;
+            float v = 0.0f;
+            if (!kGuard || lane * kChunk + idx < len) {
+                uint32_t qv = base + r[idx];
+                float edge = __fadd_rn(x0, __fmul_rn(bw, (float)qv));
+                uint32_t bits = (uint32_t)xs128p_next(s0, s1) & 0xffffffu;
+                float u = __fmul_rn((float)bits, 5.9604644775390625e-08f);  // /2^24, exact
+                v = __fadd_rn(edge, __fmul_rn(u, bw));
+                if (isPos) v = wrap(v, L);
+            }
+            o[i] = v;
+        }
+        reinterpret_cast<float4 *>(sf)[swz_chunk(lane, j)] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 template <bool kToQ>
-__global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
+__global__ void __launch_bounds__(kDecWarps * 32, 6) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
     __shared__ __align__(16) uint32_t stage[kDecWarps][kStageWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t task = (int64_t)blockIdx.x * kDecWarps + warp;
@@ -148,7 +178,8 @@ __global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams 
     const int64_t regionLen = (int64_t)(p.offsets[f + 1] - p.offsets[f]);
     const uint4 *table = reinterpret_cast<const uint4 *>(region + 64);
     const int64_t fixed = 64 + (int64_t)fd.nb * 48;
-    const uint32_t *payload = reinterpret_cast<const uint32_t *>(region + fixed);
+    const uint4 *payload = reinterpret_cast<const uint4 *>(region + fixed);
+    const int64_t payloadLen16 = (regionLen - fixed) >> 4;
 
     uint64_t s0 = 0, s1 = 0;
     if (!kToQ) {
@@ -161,57 +192,47 @@ __global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams 
     const float L = qp.width;  // the encoder's box width, not the caller's
     const float bw = __fdiv_rn(qp.maxDiff, (float)(1u << qp.depth));
 
-    const int gEnd = min(3 * fd.nb, (localTask + 1) * kRun);
-    for (int g = localTask * kRun; g < gEnd; g++) {
+    const int g0 = localTask * kRun;
+    const int gCnt = min(3 * fd.nb - g0, kRun);
+    uint4 ent = make_uint4(0u, 0u, 0u, 0u);
+    if (lane < gCnt) ent = __ldg(table + g0 + lane);
+
+    for (int k = 0; k < gCnt; k++) {
+        const int g = g0 + k;
         const int comp = g / fd.nb;
         const int b = g - comp * fd.nb;
         const int len = min(kBlockLen, fd.n - b * kBlockLen);
-        const uint4 e = __ldg(table + g);
-        const uint32_t first = e.x;
-        const uint32_t minDelta = e.y;
-        const int w = (int)e.z;
+        const uint32_t first = __shfl_sync(0xffffffffu, ent.x, k);
+        const uint32_t minDelta = __shfl_sync(0xffffffffu, ent.y, k);
+        const int w = (int)__shfl_sync(0xffffffffu, ent.z, k);
+        const uint32_t off16 = __shfl_sync(0xffffffffu, ent.w, k);
         const int nWords = (len * w + 31) >> 5;
-        const uint32_t *src = payload + (int64_t)e.w * 4;
-        if (w > kMaxWidth || fixed + (int64_t)e.w * 16 + (int64_t)nWords * 4 > regionLen) {
+        const int size16 = (nWords + 3) >> 2;
+        if (w > kMaxWidth || (int64_t)off16 + size16 > payloadLen16) {
             if (lane == 0) atomicCAS(p.error, 0, kErrPayload);
             return;
         }
 
         // ---- unpack ----
-        for (int m = lane; m < nWords; m += 32) st[skew(m)] = __ldg(src + m);
+        const uint4 *src = payload + off16;
+        for (int c = lane; c < size16; c += 32) {
+            uint4 x = ld_stream_u4(src + c);
+            const int m = c * 4;
+            st[skew(m + 0)] = x.x;
+            st[skew(m + 1)] = x.y;
+            st[skew(m + 2)] = x.z;
+            st[skew(m + 3)] = x.w;
+        }
         __syncwarp();
         uint32_t r[kChunk];
-        if (w > 0) {
-            const uint32_t mask = (1u << w) - 1u;
-            uint64_t acc = 0;
-            int fill = 0, wi = lane * w;
-#pragma unroll
-            for (int i = 0; i < kChunk; i++) {
-                if (fill < w) {
-                    uint32_t word = wi < nWords ? st[skew(wi)] : 0u;
-                    wi++;
-                    acc |= (uint64_t)word << fill;
-                    fill += 32;
-                }
-                r[i] = (uint32_t)acc & mask;
-                acc >>= w;
-                fill -= w;
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < kChunk; i++) r[i] = 0;
-        }
+        unpack_dispatch(w, r, st, lane);
         __syncwarp();
 
         // ---- inverse delta: inclusive scan of d, d[0] := 0 ----
-        uint32_t run = 0;
+        r[0] = lane ? r[0] + minDelta : 0u;
 #pragma unroll
-        for (int i = 0; i < kChunk; i++) {
-            uint32_t d = r[i] + minDelta;
-            if (lane == 0 && i == 0) d = 0;
-            run += d;
-            r[i] = run;
-        }
+        for (int i = 1; i < kChunk; i++) r[i] = r[i] + minDelta + r[i - 1];
+        const uint32_t run = r[kChunk - 1];
         uint32_t incl = run;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -227,8 +248,8 @@ __global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams 
             for (int i = 0; i < kChunk; i++) st[skew(lane * kChunk + i)] = base + r[i];
             __syncwarp();
 #pragma unroll 4
-            for (int k = 0; k < 32; k++) {
-                int el = k * 32 + lane;
+            for (int kk = 0; kk < 32; kk++) {
+                int el = kk * 32 + lane;
                 if (el < len) dst[el] = st[skew(el)];
             }
             __syncwarp();
@@ -238,40 +259,22 @@ __global__ void __launch_bounds__(kDecWarps * 32) k_unpack_dequant(DecodeParams 
         // ---- dither + de-quantise + wrap, into swizzled staging ----
         const float x0 = qp.X0[comp];
         float *sf = reinterpret_cast<float *>(st);
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            float o[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const int idx = j * 4 + i;
-                float v = 0.0f;
-                if (lane * kChunk + idx < len) {
-                    uint32_t qv = base + r[idx];
-                    float edge = __fadd_rn(x0, __fmul_rn(bw, (float)qv));
-                    uint32_t bits = (uint32_t)xs128p_next(s0, s1) & 0xffffffu;
-                    float u = __fmul_rn((float)bits, 5.9604644775390625e-08f);  // /2^24, exact
-                    v = __fadd_rn(edge, __fmul_rn(u, bw));
-                    if (isPos) v = wrap(v, L);
-                }
-                o[i] = v;
-            }
-            reinterpret_cast<float4 *>(sf)[swz_chunk(lane, j)] = make_float4(o[0], o[1], o[2], o[3]);
-        }
-        __syncwarp();
-
-        // ---- coalesced store ----
         float *dst = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
         if (len == kBlockLen && ((uintptr_t)dst & 15) == 0) {
+            dequant_block<false>(r, base, x0, bw, isPos, L, lane, len, s0, s1, sf);
+            __syncwarp();
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
-                int c = k * 32 + lane;
+            for (int kk = 0; kk < 8; kk++) {
+                int c = kk * 32 + lane;
                 float4 v = reinterpret_cast<const float4 *>(sf)[swz_chunk(c >> 3, c & 7)];
                 __stcs(reinterpret_cast<float4 *>(dst) + c, v);
             }
         } else {
+            dequant_block<true>(r, base, x0, bw, isPos, L, lane, len, s0, s1, sf);
+            __syncwarp();
 #pragma unroll 4
-            for (int k = 0; k < 32; k++) {
-                int el = k * 32 + lane;
+            for (int kk = 0; kk < 32; kk++) {
+                int el = kk * 32 + lane;
                 if (el < len) dst[el] = sf[swz_chunk(el >> 5, (el >> 2) & 7) * 4 + (el & 3)];
             }
         }

@@ -1,10 +1,28 @@
-// encode_kernels.cuh -- K1 unwrap+min/max, K1b depth, K2 quantize+delta+pack
-// with a single-pass (decoupled look-back) scan of block sizes, K2f table and
-// header finalisation. Replaces, per field, position()/velocity() of
+// encode_kernels.cuh -- the encoder: one fused kernel (k_encode) + k_finalize.
+// Replaces, per field, position()/velocity() of
 // /root/reference/src/quant.c:161-289 and the (stub) CFunc behind
 // src/funcs.c:71. HBM-bound integer/float streaming: no tensor cores.
+//
+// k_encode hands out 8192-value tiles through one dynamic ticket counter, one
+// ticket per CTA. Three kinds of tile work alternate in ticket order:
+//   A(g)  util_UndoPeriodic + util_MinMax of tile g (src/util.c:97-113, 27-46);
+//         the CTA that finishes the last A tile of a field also runs
+//         deltaToDepth (src/quant.c:186-196, 684-693) and publishes the
+//         field's quantisation parameters
+//   B(g)  `lag` tiles later: util_UniformBinIndex + delta + per-block width +
+//         util_U32UniformPack of tile g (src/util.c:173-196, 311-355). Its
+//         second read of the input hits the 126 MB L2 instead of HBM: the live
+//         window between the passes is about one field (48 MiB at 2^22
+//         particles). The packed blocks are parked in an L2-resident scratch
+//         ring and the tile's size is published.
+//   C(g)  `lag2` tiles later: a dedicated scan warp has turned the sizes into
+//         offsets by then; copy the parked blocks to their final position.
+// A ticket is only ever held by a running CTA and only waits on tickets
+// smaller than itself, so the spin-waits cannot deadlock; in steady state
+// nothing waits at all.
 #pragma once
 
+#include "bitpack.cuh"
 #include "minnow_kernels.cuh"
 
 namespace mnw {
@@ -16,19 +34,40 @@ struct EncodeParams {
     int uniformTiles;   // >0: every field has this many tiles (fast lookup)
     uint32_t *minmax;   // [nFields][3][2] ordered-uint min, ~max
     DevQuant *quant;    // [nFields]
-    uint64_t *tileState;  // [nTiles] look-back state
-    uint32_t *ticket;     // dynamic tile counter
+    uint32_t *tileAgg;    // [nTiles] kAggReady | packed size of the tile, 16-byte units
+    uint64_t *tilePrefix; // [nTiles+1] kPrefixReady | exclusive prefix, written by the scan warp
+    uint32_t *slotDone;   // [ringTiles] warps that have copied a tile out of the ring slot, cumulative
+    uint8_t *scratch;     // [ringTiles][8][kSlotBytes] packed blocks waiting for their offset
+    uint32_t *ticket;     // dynamic ticket counter
+    uint32_t *aDone;      // [nFields] A tiles finished
+    uint32_t *ready;      // [nFields] quantisation parameters published
     TmpBlock *tmp;        // [nBlocksTotal]
     uint8_t *out;
     int64_t outCap;
     uint64_t *offsets;  // [nFields+1]
     int *error;
+    int64_t nTiles;
+    int64_t nTickets;   // tickets >= nTickets mean "no more work"
+    int64_t lag;        // B(g) is issued with A(g+lag); <0: no A tiles (quant given)
+    int64_t lag2;       // C(g) is issued with B(g+lag2)
+    int64_t ringTiles;  // scratch ring capacity in tiles: a power of two, > lag2 when tiles wrap
+    int ringShift;      // log2(ringTiles)
+    unsigned long long *debugStats;  // MNWCUDA_DEBUG_STATS: look-back counters, or null
+    int debugMask;      // timing experiments only (MNWCUDA_DEBUG_MASK): 1 no look-back, 2 no stores,
+                        // 4 no pack, 8 fixed width; output bytes are wrong when set
+};
+
+// what thread 0 works out for the whole CTA from its ticket
+struct TileJob {
+    int kind;  // 0 nothing, 1 = A (min/max), 2 = B (pack)
+    int f, comp, t;
+    int64_t tile;
 };
 
 __device__ __forceinline__ void locate_tile(const EncodeParams &p, int64_t tile, int &f, int &comp,
                                             int &tileInComp) {
     if (p.uniformTiles > 0) {
-        f = (int)(tile / p.uniformTiles);
+        f = (int)((uint32_t)tile / (uint32_t)p.uniformTiles);  // tickets < 2^31
     } else {
         const DevField *fields = p.fields;
         f = find_field(p.nFields, tile, [fields](int i) { return fields[i].firstTile; });
@@ -39,79 +78,47 @@ __device__ __forceinline__ void locate_tile(const EncodeParams &p, int64_t tile,
     tileInComp = local - comp * tpc;
 }
 
-// ---------------------------------------------------------------------------
-// K1: util_UndoPeriodic (Posn only, never stored) + util_MinMax per component
-// (src/util.c:97-113, 27-46). One CTA per 8192-value tile, float4 streaming
-// loads, warp-shuffle then shared-memory reduction, one atomicMin/atomicMax
-// pair per CTA on an order-preserving integer image of the floats.
-// ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_unwrap_minmax(EncodeParams p) {
-    int f, comp, t;
-    locate_tile(p, blockIdx.x, f, comp, t);
-    const DevField fd = p.fields[f];
-    const float *base = p.in + fd.ioOff + (int64_t)comp * fd.n;
-    const int64_t start = (int64_t)t * kTileVals;
-    const int cnt = (int)min((int64_t)kTileVals, (int64_t)fd.n - start);
-    const bool isPos = fd.fieldCode == field_Posn;
-    const float L = fd.width, half = __fmul_rn(L, 0.5f);
-    const float anchor = isPos ? __ldg(base) : 0.0f;
-
-    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
-    const float *src = base + start;
-    if (cnt == kTileVals && ((uintptr_t)src & 15) == 0) {
-        const float4 *s4 = reinterpret_cast<const float4 *>(src);
-        float4 v[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = ld_stream_f4(s4 + k * 256 + threadIdx.x);
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-            float e[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                float u = isPos ? unwrap(e[i], anchor, L, half) : e[i];
-                lo = fminf(lo, u);
-                hi = fmaxf(hi, u);
-            }
-        }
-    } else {
-        for (int i = threadIdx.x; i < cnt; i += 256) {
-            float u = __ldg(src + i);
-            if (isPos) u = unwrap(u, anchor, L, half);
-            lo = fminf(lo, u);
-            hi = fmaxf(hi, u);
-        }
-    }
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
-        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
-    }
-    __shared__ float sLo[8], sHi[8];
-    if ((threadIdx.x & 31) == 0) { sLo[threadIdx.x >> 5] = lo; sHi[threadIdx.x >> 5] = hi; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int w = 1; w < 8; w++) { lo = fminf(lo, sLo[w]); hi = fmaxf(hi, sHi[w]); }
-        uint32_t *mm = p.minmax + ((int64_t)f * 3 + comp) * 2;
-        atomicMin(mm, ord_from_float(lo));
-        atomicMin(mm + 1, ~ord_from_float(hi));  // max kept inverted: both slots memset to 0xff
-    }
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// L2 eviction-priority policies for the two reads of the input (sm_100a takes
+// the priority qualifier directly only on 256-bit loads; 128-bit loads carry it
+// as a cache-hint operand)
+__device__ __forceinline__ uint64_t l2_policy_keep() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_drop() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ float4 ld_hint_f4(const float4 *p, uint64_t pol) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p), "l"(pol));
+    return r;
 }
 
 // ---------------------------------------------------------------------------
-// K1b: maxDiff and deltaToDepth per field (src/quant.c:186-196, 684-693).
+// maxDiff and deltaToDepth of one field (src/quant.c:186-196, 684-693), run by
+// a single thread once every min/max of the field is final.
 // ---------------------------------------------------------------------------
-__global__ void k_depth(EncodeParams p) {
-    int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= p.nFields) return;
+__device__ __forceinline__ void compute_quant(const EncodeParams &p, int f) {
     const DevField fd = p.fields[f];
     DevQuant q;
     float md = 0.0f;
     for (int c = 0; c < 3; c++) {
         float lo = 0.0f, hi = 0.0f;
         if (fd.n > 0) {
-            lo = float_from_ord(p.minmax[(f * 3 + c) * 2]);
-            hi = float_from_ord(~p.minmax[(f * 3 + c) * 2 + 1]);
+            lo = float_from_ord(__ldcg(p.minmax + (f * 3 + c) * 2));
+            hi = float_from_ord(~__ldcg(p.minmax + (f * 3 + c) * 2 + 1));
         }
         if (lo == 0.0f) lo = 0.0f;  // -0 -> +0 (zero canonicalisation)
         if (hi == 0.0f) hi = 0.0f;
@@ -131,283 +138,90 @@ __global__ void k_depth(EncodeParams p) {
     }
     q.depth = (uint32_t)depth;
     q.width = fd.width;
+    q.scale = __ddiv_rn((double)(1u << depth), (double)md);
     p.quant[f] = q;
 }
 
+// one thread per field: empty fields have no tiles to trigger compute_quant
+__global__ void k_depth_empty(EncodeParams p) {
+    int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= p.nFields) return;
+    if (p.fields[f].n == 0) compute_quant(p, f);
+}
+
 // ---------------------------------------------------------------------------
-// K2: one warp per 1024-value block, 8 blocks per CTA.
-//   load    8 x 128-bit coalesced loads per lane, transposed through swizzled
-//           shared memory so that each lane owns 32 consecutive values
-//   quant   util_UniformBinIndex (src/util.c:184-191)
-//   delta   d[j] = q[j]-q[j-1] (the recurrence of util_U8DeltaEncode,
-//           src/util.c:283-295, on the quantised integers), min/max by warp
-//           redux, width = bit length of (max-min)
-//   pack    util_U32UniformPack (src/util.c:333-352): each lane's 32 residuals
-//           are exactly `width` whole words
-//   place   CTA aggregate of block sizes, decoupled look-back over earlier
-//           tiles, coalesced word stores
+// A tile, phase 1 (the 8 worker warps): unwrap (Posn only, never stored) +
+// min/max. float4 streaming loads, warp-shuffle reduction, one slot per warp.
 // ---------------------------------------------------------------------------
-constexpr uint64_t kFlagAgg = 1ull << 62, kFlagPrefix = 2ull << 62, kValMask = (1ull << 62) - 1;
+__device__ __forceinline__ void minmax_phase1(const EncodeParams &p, const TileJob &job, float *sLo, float *sHi) {
+    const int f = job.f, comp = job.comp, t = job.t;
+    const DevField *fdp = p.fields + f;
+    const int n = fdp->n;
+    const float *base = p.in + fdp->ioOff + (int64_t)comp * n;
+    const int64_t start = (int64_t)t * kTileVals;
+    const int cnt = (int)min((int64_t)kTileVals, (int64_t)n - start);
+    const bool isPos = fdp->fieldCode == field_Posn;
+    const float L = fdp->width, half = __fmul_rn(L, 0.5f);
+    const float anchor = isPos ? __ldg(base) : 0.0f;
 
-template <bool kFromQ>
-__global__ void __launch_bounds__(256) k_quantize_delta_pack(EncodeParams p, const uint64_t *qIn) {
-    __shared__ __align__(16) uint32_t stage[kWarpsPerCta][kStageWords];
-    __shared__ uint32_t sSize[kWarpsPerCta];
-    __shared__ uint64_t sExcl;
-    __shared__ uint32_t sTile;
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) sTile = atomicAdd(p.ticket, 1u);
-    __syncthreads();
-    const int64_t tile = sTile;
-
-    int f, comp, t;
-    locate_tile(p, tile, f, comp, t);
-    const DevField fd = p.fields[f];
-    const DevQuant qp = p.quant[f];
-    const int b = t * kTileBlocks + warp;
-    const bool active = b < fd.nb;
-    const int len = active ? min(kBlockLen, fd.n - b * kBlockLen) : 0;
-    uint32_t *st = stage[warp];
-
-    uint32_t q[kChunk];
-    if (active) {
-        const int64_t elem = (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
-        if (!kFromQ) {
-            const float *src = p.in + fd.ioOff + elem;
-            float *sf = reinterpret_cast<float *>(st);
-            if (len == kBlockLen && ((uintptr_t)src & 15) == 0) {
-                const float4 *s4 = reinterpret_cast<const float4 *>(src);
-                float4 v[8];
+    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+    const float *src = base + start;
+    if (cnt == kTileVals && ((uintptr_t)src & 15) == 0) {
+        const float4 *s4 = reinterpret_cast<const float4 *>(src);
+        float4 v[8];
+        const uint64_t keep = l2_policy_keep();  // first read: stay in L2 for the B pass
 #pragma unroll
-                for (int k = 0; k < 8; k++) v[k] = ld_stream_f4(s4 + k * 32 + lane);
+        for (int k = 0; k < 8; k++) v[k] = ld_hint_f4(s4 + k * 256 + threadIdx.x, keep);
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    int c = k * 32 + lane;
-                    reinterpret_cast<float4 *>(sf)[swz_chunk(c >> 3, c & 7)] = v[k];
-                }
-            } else {
-                float fill = __ldg(src);
-#pragma unroll 4
-                for (int k = 0; k < 32; k++) {
-                    int e = k * 32 + lane;
-                    float v = e < len ? __ldg(src + e) : fill;
-                    sf[swz_chunk(e >> 5, (e >> 2) & 7) * 4 + (e & 3)] = v;
-                }
+        for (int k = 0; k < 8; k++) {
+            float e0 = v[k].x, e1 = v[k].y, e2 = v[k].z, e3 = v[k].w;
+            if (isPos) {
+                e0 = unwrap(e0, anchor, L, half);
+                e1 = unwrap(e1, anchor, L, half);
+                e2 = unwrap(e2, anchor, L, half);
+                e3 = unwrap(e3, anchor, L, half);
             }
-            __syncwarp();
-            const bool isPos = fd.fieldCode == field_Posn;
-            const float L = fd.width, half = __fmul_rn(L, 0.5f);
-            const float anchor = isPos ? __ldg(p.in + fd.ioOff + (int64_t)comp * fd.n) : 0.0f;
-            const float x0 = qp.X0[comp], dx = qp.maxDiff;
-            const float bins = (float)(1u << qp.depth);
-            const uint32_t top = (1u << qp.depth) - 1u;
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                float4 v = reinterpret_cast<const float4 *>(sf)[swz_chunk(lane, j)];
-                float e[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    float u = isPos ? unwrap(e[i], anchor, L, half) : e[i];
-                    q[j * 4 + i] = bin_index(u, x0, dx, bins, top);
-                }
-            }
-            __syncwarp();
-        } else {
-            // literal CFunc boundary: quantised uint64 values in (types.h:117-122)
-            const uint64_t *src = qIn + fd.ioOff + elem;
-#pragma unroll 4
-            for (int k = 0; k < 32; k++) {
-                int e = k * 32 + lane;
-                st[skew(e)] = e < len ? (uint32_t)src[e] : 0u;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < kChunk; i++) q[i] = st[skew(lane * kChunk + i)];
-            __syncwarp();
+            lo = fminf(lo, fminf(fminf(e0, e1), fminf(e2, e3)));
+            hi = fmaxf(hi, fmaxf(fmaxf(e0, e1), fmaxf(e2, e3)));
         }
     } else {
-#pragma unroll
-        for (int i = 0; i < kChunk; i++) q[i] = 0;
-    }
-
-    // ---- delta, min/max over j in [1, len) ----
-    uint32_t prevLast = __shfl_up_sync(0xffffffffu, q[kChunk - 1], 1);
-    int dmin = INT32_MAX, dmax = INT32_MIN;
-    {
-        uint32_t prev = prevLast;
-#pragma unroll
-        for (int i = 0; i < kChunk; i++) {
-            int j = lane * kChunk + i;
-            int d = (int)(q[i] - prev);
-            prev = q[i];
-            if (j >= 1 && j < len) { dmin = min(dmin, d); dmax = max(dmax, d); }
+        for (int i = threadIdx.x; i < cnt; i += 256) {
+            float u = __ldg(src + i);
+            if (isPos) u = unwrap(u, anchor, L, half);
+            lo = fminf(lo, u);
+            hi = fmaxf(hi, u);
         }
     }
-    dmin = __reduce_min_sync(0xffffffffu, dmin);
-    dmax = __reduce_max_sync(0xffffffffu, dmax);
-    if (len <= 1) { dmin = 0; dmax = 0; }
-    const uint32_t spread = (uint32_t)(dmax - dmin);
-    const int w = 32 - __clz(spread);
-    const int nWords = (len * w + 31) >> 5;
-    const uint32_t size16 = (uint32_t)((nWords + 3) >> 2);
-    const uint32_t first = __shfl_sync(0xffffffffu, q[0], 0);
-    if (lane == 0) sSize[warp] = size16;
-    __syncthreads();
-
-    // ---- publish the tile aggregate as early as possible ----
-    if (threadIdx.x == 0) {
-        uint64_t agg = 0;
 #pragma unroll
-        for (int i = 0; i < kWarpsPerCta; i++) agg += sSize[i];
-        if (tile == 0) {
-            st_volatile_u64(p.tileState, kFlagPrefix | agg);
-            sExcl = 0;
-        } else {
-            st_volatile_u64(p.tileState + tile, kFlagAgg | agg);
-        }
+    for (int d = 16; d > 0; d >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
     }
-
-    // ---- pack: lane's 32 residuals -> w words at words [lane*w, lane*w+w) ----
-    if (w > 0) {
-        uint32_t prev = prevLast;
-        uint64_t acc = 0;
-        int fill = 0, wi = lane * w;
-#pragma unroll
-        for (int i = 0; i < kChunk; i++) {
-            int j = lane * kChunk + i;
-            uint32_t r = (uint32_t)((int)(q[i] - prev) - dmin);
-            prev = q[i];
-            if (!(j >= 1 && j < len)) r = 0;
-            acc |= (uint64_t)r << fill;
-            fill += w;
-            if (fill >= 32) {
-                st[skew(wi)] = (uint32_t)acc;
-                wi++;
-                acc >>= 32;
-                fill -= 32;
-            }
-        }
-    }
-
-    // ---- look-back (warp 0) ----
-    if (warp == 0 && tile > 0) {
-        uint64_t excl = 0;
-        int64_t idx = tile - 1;
-        while (true) {
-            int64_t me = idx - lane;
-            uint64_t s = kFlagPrefix;  // virtual predecessor of tile 0: prefix 0
-            if (me >= 0) {
-                do { s = ld_volatile_u64(p.tileState + me); } while ((s >> 62) == 0);
-            }
-            uint32_t isPrefix = __ballot_sync(0xffffffffu, (s >> 62) == 2);
-            uint64_t v = s & kValMask;
-            if (isPrefix) {
-                int firstP = __ffs(isPrefix) - 1;
-                if (lane > firstP) v = 0;
-            }
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-            excl += v;
-            if (isPrefix) break;
-            idx -= 32;
-        }
-        if (lane == 0) {
-            uint64_t agg = 0;
-#pragma unroll
-            for (int i = 0; i < kWarpsPerCta; i++) agg += sSize[i];
-            st_volatile_u64(p.tileState + tile, kFlagPrefix | (excl + agg));
-            sExcl = excl;
-        }
-    }
-    __syncthreads();
-
-    if (!active) return;
-    uint64_t prefix16 = sExcl;
-    for (int i = 0; i < warp; i++) prefix16 += sSize[i];
-
-    const int64_t payloadBase = fd.fixedBase + 64 + (int64_t)fd.nb * 48;  // + 16*prefix16
-    const int64_t dstByte = payloadBase + (int64_t)(prefix16 * 16);
-    if (dstByte + (int64_t)size16 * 16 > p.outCap) {
-        if (lane == 0) atomicCAS(p.error, 0, kErrCapacity);
-        return;
-    }
-    uint32_t *dst = reinterpret_cast<uint32_t *>(p.out + dstByte);
-    const int padded = (int)size16 * 4;
-    for (int m = lane; m < padded; m += 32) dst[m] = m < nWords ? st[skew(m)] : 0u;
-    if (lane == 0) {
-        TmpBlock tb;
-        tb.first = first;
-        tb.minDelta = dmin;
-        tb.width = (uint32_t)w;
-        tb.pad = 0;
-        tb.prefix16 = prefix16;
-        p.tmp[fd.firstBlock + (int64_t)comp * fd.nb + b] = tb;
-    }
+    if ((threadIdx.x & 31) == 0) { sLo[threadIdx.x >> 5] = lo; sHi[threadIdx.x >> 5] = hi; }
 }
 
-// ---------------------------------------------------------------------------
-// K2f: after K2 every tile state holds its inclusive prefix. One thread per
-// block turns TmpBlock into the wire table entry (offset relative to the
-// field's payload base); one thread per field writes the 64-byte header and
-// the field's byte offset.
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ uint64_t prefix_before_tile(const EncodeParams &p, int64_t tile) {
-    return tile == 0 ? 0 : (p.tileState[tile - 1] & kValMask);
-}
-
-__global__ void __launch_bounds__(256) k_finalize(EncodeParams p, int64_t nBlocksTotal, int64_t nTilesTotal,
-                                                   int uniformBlocks) {
-    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g < nBlocksTotal) {
-        int f;
-        if (uniformBlocks > 0) {
-            f = (int)(g / uniformBlocks);
-        } else {
-            const DevField *fields = p.fields;
-            f = find_field(p.nFields, g, [fields](int i) { return fields[i].firstBlock; });
-        }
-        const DevField fd = p.fields[f];
-        uint64_t p0 = prefix_before_tile(p, fd.firstTile);
-        int64_t regionStart = fd.fixedBase + (int64_t)(p0 * 16);
-        TmpBlock tb = p.tmp[g];
-        int64_t entry = regionStart + 64 + (g - fd.firstBlock) * 16;
-        if (entry + 16 <= p.outCap) {
-            uint4 e = make_uint4(tb.first, (uint32_t)tb.minDelta, tb.width, (uint32_t)(tb.prefix16 - p0));
-            *reinterpret_cast<uint4 *>(p.out + entry) = e;
-        }
-    }
-    if (g <= p.nFields) {
-        int f = (int)g;
-        if (f == p.nFields) {
-            const DevField last = p.fields[f - 1];
-            int64_t fixedEnd = last.fixedBase + 64 + (int64_t)last.nb * 48;
-            p.offsets[f] = (uint64_t)fixedEnd + prefix_before_tile(p, nTilesTotal) * 16;
-            return;
-        }
-        const DevField fd = p.fields[f];
-        uint64_t p0 = prefix_before_tile(p, fd.firstTile);
-        int64_t regionStart = fd.fixedBase + (int64_t)(p0 * 16);
-        p.offsets[f] = (uint64_t)regionStart;
-        if (regionStart + 64 > p.outCap) { atomicCAS(p.error, 0, kErrCapacity); return; }
-        const DevQuant qp = p.quant[f];
-        __align__(16) MnwDiffHeader h;
-        h.Magic = algo_Diff;
-        h.Version = MNWCUDA_ALGO_VERSION;
-        h.FieldCode = fd.fieldCode;
-        h.ParticleLen = fd.n;
-        h.Depth = (uint8_t)qp.depth;
-        h.Pad[0] = h.Pad[1] = h.Pad[2] = 0;
-        h.Width = fd.fieldCode == field_Posn ? fd.width : 0.0f;
-        for (int c = 0; c < 3; c++) { h.X0[c] = qp.X0[c]; h.X1[c] = qp.X1[c]; }
-        h.BlockLen = kBlockLen;
-        h.DitherRun = MNWCUDA_DITHER_RUN;
-        h.DitherLanes = MNWCUDA_DITHER_LANES;
-        h.DitherSeed = fd.seed;
-        const uint4 *src = reinterpret_cast<const uint4 *>(&h);
-        uint4 *dst = reinterpret_cast<uint4 *>(p.out + regionStart);
-        for (int i = 0; i < 4; i++) dst[i] = src[i];
+// A tile, phase 2 (one thread, after the CTA barrier): one atomicMin/atomicMax
+// pair per tile on an order-preserving integer image of the floats; the CTA
+// that finishes a field's last tile publishes its quantisation parameters.
+__device__ __forceinline__ void minmax_phase2(const EncodeParams &p, const TileJob &job, const float *sLo,
+                                              const float *sHi) {
+    float lo = sLo[0], hi = sHi[0];
+#pragma unroll
+    for (int w = 1; w < kWarpsPerCta; w++) { lo = fminf(lo, sLo[w]); hi = fmaxf(hi, sHi[w]); }
+    const int f = job.f;
+    uint32_t *mm = p.minmax + ((int64_t)f * 3 + job.comp) * 2;
+    atomicMin(mm, ord_from_float(lo));
+    atomicMin(mm + 1, ~ord_from_float(hi));  // max kept inverted: both slots memset to 0xff
+    __threadfence();
+    uint32_t done = atomicAdd(p.aDone + f, 1u);
+    if (done == 3u * (uint32_t)p.fields[f].tilesPerComp - 1u) {
+        __threadfence();
+        compute_quant(p, f);
+        __threadfence();
+        st_release_u32(p.ready + f, 1u);
     }
 }
 
 }  // namespace mnw
+
+#include "encode_pack.cuh"

@@ -66,14 +66,20 @@ struct MnwCudaCtx {
     int64_t launches = 0;
     uint64_t ditherSeed = 0;
     Scratch fields, quant, minmax, tileState, tmp, seeds, tableOf, states, misc;
+    Scratch ring;
     Scratch ioA, ioB, ioC;  // host-buffer entry points: device staging
     uint64_t *jumpPow = nullptr;
     int *error = nullptr;     // device flag
     uint32_t *ticket = nullptr;
     cudaStream_t own = nullptr;  // stream of the synchronous host-buffer entry points
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
+    int smCount = 148;
+    int64_t encodeLag = -1;      // tiles between the A and B passes (-1: one field + margin)
+    int64_t encodeLag2 = 1024;   // tiles between parking a block (B) and placing it (C)
+    unsigned long long *debugStats = nullptr;  // MNWCUDA_DEBUG_STATS
+    int debugMask = 0;           // MNWCUDA_DEBUG_MASK: timing experiments, output bytes are wrong
     bool timing = false;         // mnwcuda_EnableKernelTiming
-    cudaEvent_t ev[10] = {};     // encode: 0..4, decode: 5..8
+    cudaEvent_t ev[10] = {};     // encode: 0..2, decode: 5..8
     bool evSet[10] = {};
 };
 
@@ -165,6 +171,14 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     CUDA_CHECK(cudaMalloc(&ctx->error, 256));
     CUDA_CHECK(cudaMemset(ctx->error, 0, 256));
     ctx->ticket = reinterpret_cast<uint32_t *>(ctx->error) + 16;
+    CUDA_CHECK(cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device));
+    if (const char *e = getenv("MNWCUDA_ENCODE_LAG")) ctx->encodeLag = atoll(e);
+    if (const char *e = getenv("MNWCUDA_DEBUG_MASK")) ctx->debugMask = atoi(e);
+    if (getenv("MNWCUDA_DEBUG_STATS")) {
+        CUDA_CHECK(cudaMalloc(&ctx->debugStats, 64));
+        CUDA_CHECK(cudaMemset(ctx->debugStats, 0, 64));
+    }
+    if (const char *e = getenv("MNWCUDA_ENCODE_LAG2")) ctx->encodeLag2 = atoll(e) < 128 ? 128 : atoll(e);
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -176,7 +190,7 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->tmp, &ctx->seeds,
-                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ioA, &ctx->ioB, &ctx->ioC};
+                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC};
     for (Scratch *s : all) s->release();
     cudaFree(ctx->jumpPow);
     cudaFree(ctx->error);
@@ -185,6 +199,14 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaStreamDestroy(ctx->copyOut);
     for (cudaEvent_t e : ctx->ev)
         if (e) cudaEventDestroy(e);
+    if (ctx->debugStats) {
+        unsigned long long h[4];
+        cudaMemcpy(h, ctx->debugStats, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[mnwcuda look-back] tiles %llu rounds/tile %.2f polls/tile %.2f ns/tile %.0f\n", h[0],
+                (double)h[1] / (double)(h[0] ? h[0] : 1), (double)h[2] / (double)(h[0] ? h[0] : 1),
+                (double)h[3] / (double)(h[0] ? h[0] : 1));
+        cudaFree(ctx->debugStats);
+    }
     delete ctx;
 }
 
@@ -198,15 +220,16 @@ extern "C" void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on) {
             if (!e) CUDA_CHECK(cudaEventCreate(&e));
 }
 
-// ms[0..3] = K1 unwrap_minmax, K1b depth, K2 quantize_delta_pack, K2f finalize
-// ms[4..6] = K3p parse_headers, K3a stream_states, K3 unpack_dequant
+// ms[0..1] = k_encode (+k_depth_empty), k_finalize; ms[2..3] unused (-1)
+// ms[4..6] = k_parse_headers, k_stream_states, k_unpack_dequant
 extern "C" int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms) {
     if (!ctx->timing) return -1;
     CUDA_CHECK(cudaSetDevice(ctx->device));
-    static const int first[7] = {0, 1, 2, 3, 5, 6, 7};
+    static const int first[7] = {0, 1, -1, -1, 5, 6, 7};
     for (int k = 0; k < 7; k++) {
         int a = first[k], b = a + 1;
         ms[k] = -1.0f;
+        if (a < 0) continue;
         if (ctx->evSet[a] && ctx->evSet[b]) {
             CUDA_CHECK(cudaEventSynchronize(ctx->ev[b]));
             CUDA_CHECK(cudaEventElapsedTime(&ms[k], ctx->ev[a], ctx->ev[b]));
@@ -236,6 +259,8 @@ struct Plan {
     std::vector<DevField> fields;
     int64_t nTiles = 0, nBlocks = 0, nTasks = 0, fixedTotal = 0, maxStreams = 0;
     int uniformTiles = 0, uniformBlocks = 0, uniformTasks = 0;
+    int64_t maxTilesPerField = 0;
+    bool hasEmpty = false;
 };
 
 int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
@@ -264,6 +289,8 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
         pl.nTiles += 3 * (int64_t)f.tilesPerComp;
         pl.nTasks += tasks;
         if (tasks * 32 > pl.maxStreams) pl.maxStreams = tasks * 32;
+        if (3 * (int64_t)f.tilesPerComp > pl.maxTilesPerField) pl.maxTilesPerField = 3 * (int64_t)f.tilesPerComp;
+        if (d.ParticleLen == 0) pl.hasEmpty = true;
         if (d.ParticleLen != h[0].ParticleLen || d.ParticleLen == 0) uniform = false;
     }
     if (uniform && nFields > 0) {
@@ -285,35 +312,39 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     p.uniformTiles = pl.uniformTiles;
     p.minmax = static_cast<uint32_t *>(ctx->minmax.need(nF * 6 * sizeof(uint32_t)));
     p.quant = static_cast<DevQuant *>(ctx->quant.need(nF * sizeof(DevQuant)));
-    p.tileState = static_cast<uint64_t *>(ctx->tileState.need((size_t)(pl.nTiles + 1) * sizeof(uint64_t)));
-    p.ticket = reinterpret_cast<uint32_t *>(p.tileState + pl.nTiles);  // zeroed with the states
+    // scratch ring for packed blocks waiting for their offset
+    p.lag2 = ctx->encodeLag2;
+    p.ringTiles = 1;
+    p.ringShift = 0;
+    while (p.ringTiles < pl.nTiles && p.ringTiles < 4 * p.lag2) { p.ringTiles <<= 1; p.ringShift++; }
+    p.scratch = static_cast<uint8_t *>(ctx->ring.need((size_t)p.ringTiles * kWarpsPerCta * kSlotBytes));
+    // one zeroed region: tile prefixes | tile sizes | ring counters | ticket | per-field A counters | ready flags
+    const size_t stateWords = (size_t)(pl.nTiles + 1) * 2 + (size_t)pl.nTiles + (size_t)p.ringTiles + 2 + 2 * nF;
+    p.tilePrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
+    p.tileAgg = reinterpret_cast<uint32_t *>(p.tilePrefix + pl.nTiles + 1);
+    p.slotDone = p.tileAgg + pl.nTiles;
+    p.ticket = p.slotDone + p.ringTiles;
+    p.aDone = p.ticket + 2;
+    p.ready = p.aDone + nF;
     p.tmp = static_cast<TmpBlock *>(ctx->tmp.need((size_t)(pl.nBlocks + 1) * sizeof(TmpBlock)));
     p.out = d_out;
     p.outCap = outCap;
     p.offsets = d_offsets;
     p.error = ctx->error;
+    p.nTiles = pl.nTiles;
+    p.lag = -1;
     // pageable source: the copy is staged before the call returns
     CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), nF * sizeof(DevField),
                                cudaMemcpyHostToDevice, s));
-    CUDA_CHECK(cudaMemsetAsync(p.tileState, 0, (size_t)(pl.nTiles + 1) * sizeof(uint64_t), s));
+    CUDA_CHECK(cudaMemsetAsync(p.tilePrefix, 0, stateWords * sizeof(uint32_t), s));
     return p;
 }
 
-void launch_pack_and_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParams &p, const uint64_t *qIn,
-                              cudaStream_t s) {
+void launch_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParams &p, cudaStream_t s) {
     const int nF = (int)pl.fields.size();
-    if (pl.nTiles > 0) {
-        if (qIn)
-            k_quantize_delta_pack<true><<<(unsigned)pl.nTiles, 256, 0, s>>>(p, qIn);
-        else
-            k_quantize_delta_pack<false><<<(unsigned)pl.nTiles, 256, 0, s>>>(p, nullptr);
-        ctx->launches++;
-    }
-    mark(ctx, 3, s);
     int64_t threads = pl.nBlocks > nF + 1 ? pl.nBlocks : nF + 1;
     k_finalize<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p, pl.nBlocks, pl.nTiles, pl.uniformBlocks);
     ctx->launches++;
-    mark(ctx, 4, s);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -335,17 +366,26 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     if (rc) return rc;
     EncodeParams p = prepare_encode(ctx, pl, d_out, outCap, d_offsets, s);
     p.in = d_in;
+    // B(g) trails A(g) by one (largest) field plus the tiles that can be in flight
+    p.lag = ctx->encodeLag >= 0 ? ctx->encodeLag : pl.maxTilesPerField + 384;
+    if (p.lag < pl.maxTilesPerField) p.lag = pl.maxTilesPerField;
+    p.debugMask = ctx->debugMask;
+    p.debugStats = ctx->debugStats;
     CUDA_CHECK(cudaMemsetAsync(p.minmax, 0xff, (size_t)nFields * 6 * sizeof(uint32_t), s));
     mark(ctx, 0, s);
+    if (pl.hasEmpty) {
+        k_depth_empty<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
+        ctx->launches++;
+    }
     if (pl.nTiles > 0) {
-        k_unwrap_minmax<<<(unsigned)pl.nTiles, 256, 0, s>>>(p);
+        p.nTickets = 2 * (pl.nTiles + p.lag + p.lag2);
+        if (p.nTickets >= (1ll << 31) - 1) return -5;
+        k_encode<false><<<(unsigned)(p.nTickets + 1), 256, 0, s>>>(p, nullptr);
         ctx->launches++;
     }
     mark(ctx, 1, s);
-    k_depth<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
-    ctx->launches++;
+    launch_finalize(ctx, pl, p, s);
     mark(ctx, 2, s);
-    launch_pack_and_finalize(ctx, pl, p, nullptr, s);
     return 0;
 }
 
@@ -427,6 +467,7 @@ void panic_on_status(MnwCudaCtx *ctx, cudaStream_t s, const char *what) {
                   "which only support 24 bits of mantissa precision.", what);  // src/quant.c:688-693
     if (err == kErrCapacity) MNW_PANIC("%s: output capacity exceeded.", what);
     if (err == kErrPayload) MNW_PANIC("%s: malformed algo_Diff payload.", what);
+    if (err == kErrRange) MNW_PANIC("%s: quantised values do not fit the declared depth.", what);
 }
 
 void *xmalloc(size_t bytes) {
@@ -666,7 +707,12 @@ extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
     if (inBytes) CUDA_CHECK(cudaMemcpyAsync(d_q, qf.Data, inBytes, cudaMemcpyHostToDevice, s));
     EncodeParams p = prepare_encode(ctx, pl, d_out, cap, d_off, s);
     CUDA_CHECK(cudaMemcpyAsync(p.quant, &dq, sizeof(dq), cudaMemcpyHostToDevice, s));
-    launch_pack_and_finalize(ctx, pl, p, d_q, s);
+    if (pl.nTiles > 0) {
+        p.nTickets = pl.nTiles + p.lag2;
+        k_encode<true><<<(unsigned)(p.nTickets + 1), 256, 0, s>>>(p, d_q);
+        ctx->launches++;
+    }
+    launch_finalize(ctx, pl, p, s);
     panic_on_status(ctx, s, "MnwCudaCompress_v0_9");
     CField cf;
     memset(&cf, 0, sizeof(cf));
