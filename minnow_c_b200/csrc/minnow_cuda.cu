@@ -13,7 +13,7 @@
 
 #include "minnow_cuda.h"
 #include "decode_kernels.cuh"
-#include "encode_persist.cuh"
+#include "encode_kernels.cuh"
 #include "gen_kernels.cuh"
 
 using namespace mnw;
@@ -65,7 +65,8 @@ struct MnwCudaCtx {
     int device = 0;
     int64_t launches = 0;
     uint64_t ditherSeed = 0;
-    Scratch fields, quant, minmax, tileState, seeds, tableOf, states, misc, overflow;
+    Scratch fields, quant, minmax, tileState, tmp, seeds, tableOf, states, misc;
+    Scratch ring;
     Scratch ioA, ioB, ioC;  // host-buffer entry points: device staging
     uint64_t *jumpPow = nullptr;
     int *error = nullptr;     // device flag
@@ -73,10 +74,10 @@ struct MnwCudaCtx {
     cudaStream_t own = nullptr;  // stream of the synchronous host-buffer entry points
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     int smCount = 148;
-    int64_t encodeLag = -1;      // tiles between the A and B passes (-1: one field + encodeMargin)
-    int64_t encodeMargin = 1024; // tiles of slack so that a field's parameters are ready when its B tiles start
-    EncodeParams lastEnc;        // most recent encode launch (diagnostics on a device-side timeout)
-    bool haveLastEnc = false;
+    int64_t encodeLag = -1;      // tiles between the A and B passes (-1: one field + margin)
+    int64_t encodeLag2 = 1024;   // tiles between parking a block (B) and placing it (C)
+    unsigned long long *debugStats = nullptr;  // MNWCUDA_DEBUG_STATS
+    int debugMask = 0;           // MNWCUDA_DEBUG_MASK: timing experiments, output bytes are wrong
     bool timing = false;         // mnwcuda_EnableKernelTiming
     cudaEvent_t ev[10] = {};     // encode: 0..2, decode: 5..8
     bool evSet[10] = {};
@@ -172,9 +173,12 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     ctx->ticket = reinterpret_cast<uint32_t *>(ctx->error) + 16;
     CUDA_CHECK(cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device));
     if (const char *e = getenv("MNWCUDA_ENCODE_LAG")) ctx->encodeLag = atoll(e);
-    if (const char *e = getenv("MNWCUDA_ENCODE_MARGIN")) ctx->encodeMargin = atoll(e) < 0 ? 0 : atoll(e);
-    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
-    CUDA_CHECK(cudaFuncSetAttribute(k_encode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    if (const char *e = getenv("MNWCUDA_DEBUG_MASK")) ctx->debugMask = atoi(e);
+    if (getenv("MNWCUDA_DEBUG_STATS")) {
+        CUDA_CHECK(cudaMalloc(&ctx->debugStats, 64));
+        CUDA_CHECK(cudaMemset(ctx->debugStats, 0, 64));
+    }
+    if (const char *e = getenv("MNWCUDA_ENCODE_LAG2")) ctx->encodeLag2 = atoll(e) < 128 ? 128 : atoll(e);
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -185,8 +189,8 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
-    Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->seeds,
-                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->overflow, &ctx->ioA, &ctx->ioB, &ctx->ioC};
+    Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->tmp, &ctx->seeds,
+                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC};
     for (Scratch *s : all) s->release();
     cudaFree(ctx->jumpPow);
     cudaFree(ctx->error);
@@ -195,6 +199,14 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaStreamDestroy(ctx->copyOut);
     for (cudaEvent_t e : ctx->ev)
         if (e) cudaEventDestroy(e);
+    if (ctx->debugStats) {
+        unsigned long long h[4];
+        cudaMemcpy(h, ctx->debugStats, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[mnwcuda look-back] tiles %llu rounds/tile %.2f polls/tile %.2f ns/tile %.0f\n", h[0],
+                (double)h[1] / (double)(h[0] ? h[0] : 1), (double)h[2] / (double)(h[0] ? h[0] : 1),
+                (double)h[3] / (double)(h[0] ? h[0] : 1));
+        cudaFree(ctx->debugStats);
+    }
     delete ctx;
 }
 
@@ -232,28 +244,6 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
     CUDA_CHECK(cudaMemcpyAsync(&err, ctx->error, sizeof(int), cudaMemcpyDeviceToHost, s));
     CUDA_CHECK(cudaStreamSynchronize(s));
     if (err != 0) {
-        if (err == kErrTimeout) {
-            int info[4] = {0, 0, 0, 0};
-            CUDA_CHECK(cudaMemcpy(info, ctx->error, sizeof(info), cudaMemcpyDeviceToHost));
-            fprintf(stderr, "[mnwcuda] device-side wait timed out: site %d, tile %d\n", info[1], info[2]);
-            if (ctx->haveLastEnc) {
-                const EncodeParams &q = ctx->lastEnc;
-                uint32_t st[4] = {0, 0, 0, 0};
-                cudaMemcpy(&st[0], q.ticket, 4, cudaMemcpyDeviceToHost);
-                cudaMemcpy(&st[1], q.aDone, 4, cudaMemcpyDeviceToHost);
-                cudaMemcpy(&st[2], q.ready, 4, cudaMemcpyDeviceToHost);
-                fprintf(stderr, "[mnwcuda] nTiles %lld nTickets %lld lag %lld | ticket %u aDone[0] %u ready[0] %u\n",
-                        (long long)q.nTiles, (long long)q.nTickets, (long long)q.lag, st[0], st[1], st[2]);
-                int64_t show = q.nTiles < 32 ? q.nTiles : 32;
-                std::vector<uint32_t> agg((size_t)show);
-                std::vector<uint64_t> pre((size_t)show + 1);
-                cudaMemcpy(agg.data(), q.tileAgg, (size_t)show * 4, cudaMemcpyDeviceToHost);
-                cudaMemcpy(pre.data(), q.tilePrefix, (size_t)(show + 1) * 8, cudaMemcpyDeviceToHost);
-                for (int64_t i = 0; i < show; i++)
-                    fprintf(stderr, "  tile %lld agg %08x prefix %016llx\n", (long long)i, agg[(size_t)i],
-                            (unsigned long long)pre[(size_t)i]);
-            }
-        }
         CUDA_CHECK(cudaMemsetAsync(ctx->error, 0, sizeof(int), s));
         CUDA_CHECK(cudaStreamSynchronize(s));
     }
@@ -291,7 +281,7 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
         f.fieldCode = d.FieldCode;
         f.delta = d.Delta;
         f.width = d.Width;
-        f.tilesPerComp = (f.nb + kEncTileBlocks - 1) / kEncTileBlocks;
+        f.tilesPerComp = (f.nb + kTileBlocks - 1) / kTileBlocks;
         f.seed = d.DitherSeed;
         int64_t tasks = (3 * (int64_t)f.nb + kRun - 1) / kRun;
         pl.fixedTotal += mnwcuda_FieldFixedBytes(d.ParticleLen);
@@ -322,15 +312,21 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     p.uniformTiles = pl.uniformTiles;
     p.minmax = static_cast<uint32_t *>(ctx->minmax.need(nF * 6 * sizeof(uint32_t)));
     p.quant = static_cast<DevQuant *>(ctx->quant.need(nF * sizeof(DevQuant)));
-    // one zeroed region: tile prefixes | tile sizes | ticket | per-field A counters | ready flags
-    const size_t stateWords = (size_t)(pl.nTiles + 1) * 2 + (size_t)pl.nTiles + 2 + 2 * nF;
+    // scratch ring for packed blocks waiting for their offset
+    p.lag2 = ctx->encodeLag2;
+    p.ringTiles = 1;
+    p.ringShift = 0;
+    while (p.ringTiles < pl.nTiles && p.ringTiles < 4 * p.lag2) { p.ringTiles <<= 1; p.ringShift++; }
+    p.scratch = static_cast<uint8_t *>(ctx->ring.need((size_t)p.ringTiles * kWarpsPerCta * kSlotBytes));
+    // one zeroed region: tile prefixes | tile sizes | ring counters | ticket | per-field A counters | ready flags
+    const size_t stateWords = (size_t)(pl.nTiles + 1) * 2 + (size_t)pl.nTiles + (size_t)p.ringTiles + 2 + 2 * nF;
     p.tilePrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
     p.tileAgg = reinterpret_cast<uint32_t *>(p.tilePrefix + pl.nTiles + 1);
-    p.ticket = p.tileAgg + pl.nTiles;
+    p.slotDone = p.tileAgg + pl.nTiles;
+    p.ticket = p.slotDone + p.ringTiles;
     p.aDone = p.ticket + 2;
     p.ready = p.aDone + nF;
-    p.overflow = static_cast<uint32_t *>(ctx->overflow.need((size_t)ctx->smCount * kEncWarps * 2 * kEncTileBlocks *
-                                                           kEncSlotWords * sizeof(uint32_t)));
+    p.tmp = static_cast<TmpBlock *>(ctx->tmp.need((size_t)(pl.nBlocks + 1) * sizeof(TmpBlock)));
     p.out = d_out;
     p.outCap = outCap;
     p.offsets = d_offsets;
@@ -344,21 +340,10 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     return p;
 }
 
-void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, bool fromQ, cudaStream_t s) {
-    // one persistent CTA per SM; fewer when the batch is tiny
-    int64_t ctas = (p.nTickets + kEncWarps - 1) / kEncWarps + 1;
-    if (ctas > ctx->smCount) ctas = ctx->smCount;
-    ctx->lastEnc = p;
-    ctx->haveLastEnc = true;
-    if (fromQ) k_encode<true><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(p);
-    else k_encode<false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(p);
-    ctx->launches++;
-    CUDA_CHECK(cudaGetLastError());
-}
-
 void launch_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParams &p, cudaStream_t s) {
     const int nF = (int)pl.fields.size();
-    k_finalize<<<(unsigned)((nF + 1 + 127) / 128), 128, 0, s>>>(p, pl.fixedTotal);
+    int64_t threads = pl.nBlocks > nF + 1 ? pl.nBlocks : nF + 1;
+    k_finalize<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p, pl.nBlocks, pl.nTiles, pl.uniformBlocks);
     ctx->launches++;
     CUDA_CHECK(cudaGetLastError());
 }
@@ -382,8 +367,10 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     EncodeParams p = prepare_encode(ctx, pl, d_out, outCap, d_offsets, s);
     p.in = d_in;
     // B(g) trails A(g) by one (largest) field plus the tiles that can be in flight
-    p.lag = ctx->encodeLag >= 0 ? ctx->encodeLag : pl.maxTilesPerField + ctx->encodeMargin;
+    p.lag = ctx->encodeLag >= 0 ? ctx->encodeLag : pl.maxTilesPerField + 384;
     if (p.lag < pl.maxTilesPerField) p.lag = pl.maxTilesPerField;
+    p.debugMask = ctx->debugMask;
+    p.debugStats = ctx->debugStats;
     CUDA_CHECK(cudaMemsetAsync(p.minmax, 0xff, (size_t)nFields * 6 * sizeof(uint32_t), s));
     mark(ctx, 0, s);
     if (pl.hasEmpty) {
@@ -391,9 +378,10 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
         ctx->launches++;
     }
     if (pl.nTiles > 0) {
-        p.nTickets = 2 * (pl.nTiles + p.lag);
+        p.nTickets = 2 * (pl.nTiles + p.lag + p.lag2);
         if (p.nTickets >= (1ll << 31) - 1) return -5;
-        launch_encode(ctx, p, false, s);
+        k_encode<false><<<(unsigned)(p.nTickets + 1), 256, 0, s>>>(p, nullptr);
+        ctx->launches++;
     }
     mark(ctx, 1, s);
     launch_finalize(ctx, pl, p, s);
@@ -480,7 +468,6 @@ void panic_on_status(MnwCudaCtx *ctx, cudaStream_t s, const char *what) {
     if (err == kErrCapacity) MNW_PANIC("%s: output capacity exceeded.", what);
     if (err == kErrPayload) MNW_PANIC("%s: malformed algo_Diff payload.", what);
     if (err == kErrRange) MNW_PANIC("%s: quantised values do not fit the declared depth.", what);
-    if (err == kErrTimeout) MNW_PANIC("%s: a device-side wait timed out (internal error).", what);
 }
 
 void *xmalloc(size_t bytes) {
@@ -721,9 +708,9 @@ extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
     EncodeParams p = prepare_encode(ctx, pl, d_out, cap, d_off, s);
     CUDA_CHECK(cudaMemcpyAsync(p.quant, &dq, sizeof(dq), cudaMemcpyHostToDevice, s));
     if (pl.nTiles > 0) {
-        p.nTickets = pl.nTiles;
-        p.qIn = d_q;
-        launch_encode(ctx, p, true, s);
+        p.nTickets = pl.nTiles + p.lag2;
+        k_encode<true><<<(unsigned)(p.nTickets + 1), 256, 0, s>>>(p, d_q);
+        ctx->launches++;
     }
     launch_finalize(ctx, pl, p, s);
     panic_on_status(ctx, s, "MnwCudaCompress_v0_9");
