@@ -121,7 +121,55 @@ EXPORTS = {
                                             C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
+class _Seq(C.Structure):
+    _fields_ = [("Data", C.c_void_p), ("Len", C.c_int32), ("Cap", C.c_int32)]
+
+
+class Register(C.Structure):  # include/minnow_register.h (src/register.h:9-13)
+    _fields_ = [("Algo", _Seq), ("Version", _Seq), ("Funcs", _Seq)]
+
+
+class RegisterFuncs(C.Structure):  # src/register.h:15-22
+    _fields_ = [("CFunc", C.c_void_p), ("CAlloc", C.c_void_p), ("CFree", C.c_void_p),
+                ("DFunc", C.c_void_p), ("DAlloc", C.c_void_p), ("DFree", C.c_void_p)]
+
+
+class Compressor(C.Structure):
+    _fields_ = [("Buffer", C.c_void_p), ("CFunc", C.c_void_p)]
+
+
+class Decompressor(C.Structure):
+    _fields_ = [("Buffer", C.c_void_p), ("DFunc", C.c_void_p)]
+
+
+class Seg(C.Structure):
+    _fields_ = [("Fields", C.POINTER(Field)), ("FieldLen", C.c_int32)]
+
+
+class CSeg(C.Structure):
+    _fields_ = [("Fields", C.POINTER(CField)), ("FieldLen", C.c_int32)]
+
+
+HOST_EXPORTS = {
+    "Register_New": (Register, []),
+    "Register_Free": (None, [Register]),
+    "Register_Add": (None, [Register, C.c_uint32, C.c_uint32, RegisterFuncs]),
+    "Register_GetCompressor": (Compressor, [Register, C.c_uint32, C.c_uint32]),
+    "Register_GetDecompressor": (Decompressor, [Register, C.c_uint32, C.c_uint32]),
+    "Register_FreeCompressor": (None, [Register, C.c_uint32, C.c_uint32, Compressor]),
+    "Register_FreeDecompressor": (None, [Register, C.c_uint32, C.c_uint32, Decompressor]),
+    "Register_Supports": (C.c_bool, [Register, C.c_uint32, C.c_uint32]),
+    "Register_Newest": (C.c_uint32, [Register, C.c_uint32]),
+    "MnwSeg_Encode": (CSeg, [Seg]),
+    "MnwSeg_Decode": (Seg, [CSeg]),
+    "MnwCSeg_Free": (None, [CSeg]),
+    "MnwSeg_Free": (None, [Seg]),
+    "MnwChecksum": (C.c_uint32, [C.c_void_p, C.c_int64]),
+    "MnwSeg_SetDitherSeed": (None, [C.c_uint64]),
+}
+
 _lib = None
+_host = None
 _libc = C.CDLL(None)
 _libc.free.argtypes = [C.c_void_p]
 
@@ -140,6 +188,22 @@ def lib():
             fn.argtypes = args
         _lib = handle
     return _lib
+
+
+def host_lib():
+    """The loaded libminnow_host.so (registry + segment flow, host-side C)."""
+    global _host
+    if _host is None:
+        lib()  # libminnow_cuda.so first: the host library links against it
+        if not os.path.exists(HOST_LIB_PATH):
+            raise RuntimeError("libminnow_host.so is not built (run __graft_entry__.build())")
+        handle = C.CDLL(HOST_LIB_PATH)
+        for name, (res, args) in HOST_EXPORTS.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _host = handle
+    return _host
 
 
 def field_bound(n):
