@@ -261,6 +261,7 @@ def run_b200(args):
     import torch.distributed as dist
 
     import minnow_c_b200 as mc
+    from minnow_c_b200 import sharded
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -289,7 +290,6 @@ def run_b200(args):
     d_out = torch.empty(cap, dtype=torch.uint8, device=dev)
     d_off = torch.zeros(nf + 1, dtype=torch.int64, device=dev)
     d_dec = torch.empty_like(d_in)
-    sizes = torch.zeros(world, dtype=torch.int64, device=dev)
     torch.cuda.synchronize()
 
     def step(record=None):
@@ -299,8 +299,7 @@ def run_b200(args):
         if world > 1:
             # output placement of the sharded stream: all-gather of per-rank
             # compressed sizes, exclusive prefix = this rank's base offset
-            dist.all_gather_into_tensor(sizes, d_off[nf:nf + 1])
-            base = torch.cumsum(sizes, 0)[rank] - sizes[rank]  # noqa: F841
+            _sizes, _base = sharded.exchange_sizes(d_off[nf:nf + 1])
         if record:
             record[1].record()
         if args.encode_only:
@@ -365,6 +364,10 @@ def run_b200(args):
     # ---- e2e through the host-buffer C ABI (pinned host memory) ----
     e2e = None if args.no_e2e else run_e2e(torch, mc, codec, d_in, args, n_gpus, dev, world)
 
+    gather = None
+    if world > 1 and not args.no_gather:
+        gather = run_gather(torch, dist, sharded, d_out, d_off, nf, dev, rank)
+
     value = n_gpus * 2 * raw_bytes * args.steps / (tot_ms * 1e-3) / 1e9
     enc_gbs = n_gpus * raw_bytes * args.steps / (enc_ms * 1e-3) / 1e9
     dec_gbs = n_gpus * raw_bytes * args.steps / (dec_ms * 1e-3) / 1e9
@@ -414,10 +417,43 @@ def run_b200(args):
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clk, "check": check, "wall_s": t_wall,
     }
+    if gather is not None:
+        line["gather"] = gather
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def run_gather(torch, dist, sharded, d_out, d_off, nf, dev, rank):
+    """Gather of the packed stream to rank 0 over NVLink (reported
+    on its own, it is not part of the encode/decode metric). Device-timed."""
+    sizes, _ = sharded.exchange_sizes(d_off[nf:nf + 1])
+    sizes_h = [int(v) for v in sizes.cpu()]
+    total = sum(sizes_h)
+    free = torch.cuda.mem_get_info(dev)[0]
+    if rank == 0 and total > free - (2 << 30):
+        ok = torch.zeros(1, device=dev)
+    else:
+        ok = torch.ones(1, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if float(ok.item()) == 0.0:
+        return {"skipped": "sink has no room for the whole stream", "bytes": total}
+    local = d_out[:sizes_h[rank]]
+    sharded.gather_stream(local, sizes_h, dst=0)  # warm-up
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = sharded.gather_stream(local, sizes_h, dst=0)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    del out
+    moved = total - sizes_h[0]
+    return {"ms": float(ms.item()), "bytes_into_sink": moved, "gbs": moved / (float(ms.item()) * 1e-3) / 1e9,
+            "note": "ncclSend/Recv of each rank's packed slab to rank 0; not part of the metric"}
 
 
 def roundtrip_check(torch, d_in, d_dec, fields, seg):
@@ -534,6 +570,7 @@ def main():
     ap.add_argument("--encode-only", action="store_true", help="kernel experiments: time encode only, no checks")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer e2e leg (kernel experiments)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-gather", action="store_true", help="N>1: skip the (separately reported) stream gather")
     args = ap.parse_args()
     if args.steps < 1:
         args.steps = 1
