@@ -1,0 +1,146 @@
+// enc_common.cuh -- constants, parameters and small helpers of the encoder
+// (k_encode + k_finalize). Replaces, per field, position()/velocity() of
+// /root/reference/src/quant.c:161-289 and the (stub) CFunc behind
+// src/funcs.c:71. HBM-bound float/integer streaming: no tensor cores.
+//
+// Work is cut into 1024-value blocks. Blocks are numbered over the whole batch
+// (field-major, then component, then block). Global work "groups" of 32 slots
+// are handed out by one ticket counter: slots 0..15 of group g are the A work
+// (unwrap + min/max) of blocks 16g..16g+15, slots 16..31 the B work (quantise +
+// delta + width + pack) of blocks 16(g-lagG)..16(g-lagG)+15 -- lagG groups
+// later, when the field's parameters are known and, with luck, the block is
+// still in L2.
+#pragma once
+
+#include <cuda.h>
+
+#include "bitpack.cuh"
+#include "minnow_kernels.cuh"
+
+namespace mnw {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kEncWarps = 16;        // per CTA (one CTA per SM): producer, 14 consumers, scan warp (CTA 0 only)
+constexpr int kEncConsumers = 14;
+constexpr int kEncStages = 48;       // input ring: 4 KiB blocks per SM (TMA, 128-byte swizzle)
+constexpr int kEncStageBytes = 4096;
+constexpr int kGroupSlots = 32;      // slots per ticket
+constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
+constexpr int kEncRingOff = 0;
+constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
+constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 32 + 16;
+constexpr int kEncSmemBytes = kEncCtrlOff + kEncCtrlBytes;
+constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bits x 1024, 16-byte padded
+
+constexpr uint32_t kAggReady = 0x80000000u;
+constexpr uint64_t kPrefixReady = 1ull << 63;
+constexpr uint32_t kQBias = 0x4b000000u;  // bit pattern of 2^23: trunc by add.rz keeps it in the exponent
+
+enum : int { kWorkNop = 0, kWorkA = 1, kWorkB = 2, kWorkStop = 3 };
+
+struct BlockRec {  // what placement needs to know about a parked block
+    uint32_t first;
+    int32_t minDelta;
+    uint32_t width;
+    uint32_t size16;
+};
+
+struct EncodeParams {
+    const float *in;
+    const uint64_t *qIn;   // literal CFunc boundary: quantised values in, or null
+    const DevField *fields;
+    int nFields;
+    int uniformBlocks;     // >0: every field has this many blocks (fast lookup)
+    uint32_t *minmax;      // [nFields][3][2] ordered-uint min, ~max
+    DevQuant *quant;       // [nFields]
+    uint32_t *blkAgg;      // [nBlocks] kAggReady | packed size of the block, 16-byte units
+    uint64_t *blkPrefix;   // [nBlocks+1] kPrefixReady | exclusive prefix, written by the scan warp
+    uint32_t *ticket;      // group ticket counter
+    uint32_t *aDone;       // [nFields] A blocks finished
+    uint32_t *ready;       // [nFields] quantisation parameters published
+    uint32_t *slotDone;    // [ringBlocks] placements out of the slot, cumulative
+    BlockRec *rec;         // [ringBlocks]
+    uint32_t *scratch;     // [ringBlocks][kSlotWords] packed blocks waiting for their offset
+    int64_t ringBlocks;    // a power of two > lag2
+    int ringShift;
+    int64_t lag2;          // block b is placed by whoever packs block b+lag2
+    int64_t tmaShift;      // floats between the tensor map's 128-byte aligned base and `in`; <0: no TMA
+    int64_t tmaRows;       // rows of 32 floats covered by the tensor map
+    uint8_t *out;
+    int64_t outCap;
+    uint64_t *offsets;     // [nFields+1]
+    int *error;
+    int64_t nBlocks;
+    int64_t nGroups;       // tickets >= nGroups mean "no more work"
+    int64_t lagG;          // B of group g-lagG rides with A of group g; <0: no A work (quant given)
+    unsigned long long *stats;  // MNWCUDA_ENCODE_STATS: per-phase clock totals over all warps, or null
+};
+
+// ---- memory-ordering helpers ----
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t ld_acquire_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(uint64_t *p, uint64_t v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_keep() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_drop() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void st_stream_u4(uint4 *p, uint4 v) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+// every spin-wait gives up after a fraction of a second and raises kErrTimeout
+// instead of hanging the device: error[1] = site, error[2..3] = block
+constexpr uint32_t kSpinLimit = 1u << 19;
+__device__ __noinline__ void spin_timeout(int *error, int site, int64_t blk) {
+    if (atomicCAS(error, 0, kErrTimeout) == 0) {
+        error[1] = site;
+        error[2] = (int)(blk & 0xffffffff);
+        error[3] = (int)(blk >> 32);
+    }
+}
+
+// global block index -> field, component, block within the component
+__device__ __forceinline__ void locate_block(const EncodeParams &p, int64_t blk, int &f, int &comp, int &b) {
+    if (p.uniformBlocks > 0) {
+        f = (int)((uint32_t)blk / (uint32_t)p.uniformBlocks);
+    } else {
+        const DevField *fields = p.fields;
+        f = find_field(p.nFields, blk, [fields](int i) { return fields[i].firstBlock; });
+    }
+    const int local = (int)(blk - p.fields[f].firstBlock);
+    const int nb = p.fields[f].nb;
+    comp = local / nb;
+    b = local - comp * nb;
+}
+
+}  // namespace mnw

@@ -1,0 +1,196 @@
+// enc_consume.cuh -- B work, placement, the kernel and k_finalize. Included by
+// enc_kernel.cuh.
+#pragma once
+
+#include "enc_kernel.cuh"
+
+namespace mnw {
+
+__device__ __forceinline__ void release_stage(const RingCtrl &rc, int s, bool wrote, int lane) {
+    __syncwarp();
+    if (lane == 0) {
+        if (wrote) fence_proxy_async();  // generic-proxy writes before the TMA's next fill
+        mbar_arrive(rc.empty + s);
+    }
+}
+
+// quantisation parameters of the component a consumer is working on
+struct QuantCache {
+    int f, comp;  // -1: empty
+    float x0;
+    double scale;
+    uint32_t top;
+    bool biased, isPos;
+    Unwrap uw;
+};
+
+template <bool kFromQ>
+__device__ __forceinline__ void load_quant(const EncodeParams &p, const WorkDesc &d, QuantCache &qc, MinMaxAcc &acc,
+                                           int lane) {
+    if (qc.f == d.f && qc.comp == d.comp) return;
+    const DevField *fdp = p.fields + d.f;
+    qc.f = d.f;
+    qc.comp = d.comp;
+    qc.isPos = fdp->fieldCode == field_Posn;
+    qc.uw.tHi = qc.uw.tLo = qc.uw.L = 0.0f;
+    qc.x0 = 0.0f;
+    qc.scale = 0.0;
+    qc.top = 0;
+    qc.biased = false;
+    if (kFromQ) return;
+    if (p.lagG >= 0 && ld_acquire_u32(p.ready + d.f) == 0u) {
+        acc_flush(p, acc, lane);  // never wait while holding what others wait for
+        uint32_t spins = 0;
+        while (ld_acquire_u32(p.ready + d.f) == 0u) {
+            __nanosleep(100);
+            if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); break; }
+        }
+    }
+    const DevQuant *qp = p.quant + d.f;  // written during this launch: read through L2
+    qc.x0 = __ldcg(&qp->X0[d.comp]);
+    qc.scale = __ldcg(&qp->scale);
+    const uint32_t depth = __ldcg(&qp->depth);
+    qc.top = (1u << depth) - 1u;
+    qc.biased = depth <= 23;
+    if (qc.isPos) qc.uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * fdp->n), fdp->width);
+}
+
+// ---------------------------------------------------------------------------
+// placement of block `pl`: scratch slot -> final position, table entry
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void place_block(const EncodeParams &p, int64_t pl, uint64_t preW, MinMaxAcc &acc,
+                                            int lane) {
+    if (!(preW & kPrefixReady)) {
+        acc_flush(p, acc, lane);
+        uint32_t spins = 0;
+        while (!((preW = ld_relaxed_u64(p.blkPrefix + pl)) & kPrefixReady)) {
+            __nanosleep(200);
+            if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); break; }
+        }
+    }
+    __threadfence();  // acquire: the block's record and scratch slot were released before its size
+    const uint64_t pre = preW & ~kPrefixReady;
+    int f, comp, b;
+    locate_block(p, pl, f, comp, b);
+    const DevField *fdp = p.fields + f;
+    const int nb = fdp->nb;
+    uint64_t p0w = ld_relaxed_u64(p.blkPrefix + fdp->firstBlock);  // published no later than `pre`, bar reordering
+    for (uint32_t spins = 0; !(p0w & kPrefixReady) && spins < kSpinLimit; spins++)
+        p0w = ld_relaxed_u64(p.blkPrefix + fdp->firstBlock);
+    const uint64_t p0 = p0w & ~kPrefixReady;
+    const int64_t rp = pl & (p.ringBlocks - 1);
+    const uint4 rv = __ldcg(reinterpret_cast<const uint4 *>(p.rec + rp));
+    const uint32_t size16 = rv.w;
+    const int64_t tableBase = fdp->fixedBase + (int64_t)(p0 * 16) + 64;
+    const int64_t dstByte = tableBase + (int64_t)nb * 48 + (int64_t)((pre - p0) * 16);
+    if (dstByte + (int64_t)size16 * 16 > p.outCap) {
+        if (lane == 0) atomicCAS(p.error, 0, kErrCapacity);
+    } else {
+        const uint4 *slot = reinterpret_cast<const uint4 *>(p.scratch + rp * kSlotWords);
+        uint4 *dst = reinterpret_cast<uint4 *>(p.out + dstByte);
+        for (int c = lane; c < (int)size16; c += 32) st_stream_u4(dst + c, __ldcg(slot + c));
+        if (lane == 0) {
+            const uint4 e = make_uint4(rv.x, rv.y, rv.z, (uint32_t)(pre - p0));
+            *reinterpret_cast<uint4 *>(p.out + tableBase + ((int64_t)comp * nb + b) * 16) = e;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) atomicAdd(p.slotDone + rp, 1u);
+}
+
+// ---------------------------------------------------------------------------
+// B work on block d.blk (blk >= nBlocks: placement only)
+// ---------------------------------------------------------------------------
+template <bool kFromQ>
+__device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d, float *stage, const RingCtrl &rc,
+                                        int s, QuantCache &qc, MinMaxAcc &acc, int lane) {
+    const int64_t blk = d.blk;
+    const int64_t pl = blk - p.lag2;
+    // loads whose results are needed late go out first
+    uint64_t preW = 0;
+    if (pl >= 0) preW = ld_relaxed_u64(p.blkPrefix + pl);
+    if (blk >= p.nBlocks) {
+        release_stage(rc, s, false, lane);
+        if (pl >= 0 && pl < p.nBlocks) place_block(p, pl, preW, acc, lane);
+        return;
+    }
+    const int64_t ringPos = blk & (p.ringBlocks - 1);
+    const uint32_t tenants = (uint32_t)(blk >> p.ringShift);  // earlier users of the scratch slot
+    uint32_t freed = ld_acquire_u32(p.slotDone + ringPos);
+    load_quant<kFromQ>(p, d, qc, acc, lane);
+
+    const int len = d.len;
+    uint32_t q[kChunk];
+    if (kFromQ) {
+        // literal CFunc boundary: quantised uint64 values in (types.h:117-122)
+        const DevField *fdp = p.fields + d.f;
+        const uint64_t *qsrc = p.qIn + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
+#pragma unroll
+        for (int i = 0; i < kChunk; i++) {
+            const int e = lane * kChunk + i;
+            q[i] = e < len ? (uint32_t)qsrc[e] : 0u;
+        }
+    } else {
+        if (d.slow) {
+            // ragged or unaligned block: plain loads into the stage, same swizzled layout
+            const DevField *fdp = p.fields + d.f;
+            const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
+            const float fill = __ldg(src);
+#pragma unroll 4
+            for (int k = 0; k < 32; k++) {
+                const int e = k * 32 + lane;
+                const float x = e < len ? __ldg(src + e) : fill;
+                stage[swz_chunk(e >> 5, (e >> 2) & 7) * 4 + (e & 3)] = x;
+            }
+            __syncwarp();
+        }
+        if (qc.isPos) {
+            if (qc.biased) quantise32<true, true>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
+            else quantise32<true, false>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
+        } else {
+            if (qc.biased) quantise32<false, true>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
+            else quantise32<false, false>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
+        }
+    }
+
+    BlockStats bs = delta_width(q, len, lane, p.error);
+    if (!kFromQ && qc.biased) bs.first -= kQBias;
+    const int nWords = (len * bs.w + 31) >> 5;
+    const uint32_t size16 = (uint32_t)((nWords + 3) >> 2);
+
+    // pack through the block's own stage (its values are in registers by now)
+    uint32_t *tmp = reinterpret_cast<uint32_t *>(stage);
+    __syncwarp();
+    if (bs.w > 0) pack_dispatch(bs.w, q, tmp, lane);
+    __syncwarp();
+    if (freed < tenants) {  // the slot's previous tenant has not been placed yet (rare)
+        acc_flush(p, acc, lane);
+        uint32_t spins = 0;
+        while ((freed = ld_acquire_u32(p.slotDone + ringPos)) < tenants) {
+            __nanosleep(200);
+            if (++spins > kSpinLimit) { spin_timeout(p.error, 8, blk); break; }
+        }
+    }
+    uint4 *slot = reinterpret_cast<uint4 *>(p.scratch + ringPos * kSlotWords);
+    for (int c = lane; c < (int)size16; c += 32) {
+        const int m = c * 4;
+        uint4 o;
+        o.x = tmp[skew(m)];
+        o.y = m + 1 < nWords ? tmp[skew(m + 1)] : 0u;
+        o.z = m + 2 < nWords ? tmp[skew(m + 2)] : 0u;
+        o.w = m + 3 < nWords ? tmp[skew(m + 3)] : 0u;
+        slot[c] = o;
+    }
+    if (lane == 0)
+        *reinterpret_cast<uint4 *>(p.rec + ringPos) = make_uint4(bs.first, (uint32_t)bs.dmin, (uint32_t)bs.w, size16);
+    release_stage(rc, s, true, lane);  // includes __syncwarp: every lane's slot stores precede lane 0's release
+    if (lane == 0) {
+        __threadfence();
+        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.blkAgg + blk), "r"(kAggReady | size16) : "memory");
+    }
+    if (pl >= 0) place_block(p, pl, preW, acc, lane);
+}
+
+}  // namespace mnw
+
+#include "enc_entry.cuh"

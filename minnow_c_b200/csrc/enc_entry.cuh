@@ -1,0 +1,117 @@
+// enc_entry.cuh -- the kernels' entry points. Included by enc_consume.cuh.
+#pragma once
+
+#include "enc_consume.cuh"
+
+namespace mnw {
+
+// ---------------------------------------------------------------------------
+// k_encode: warp 0 = producer, warps 1..14 = consumers, warp 15 = the scan warp
+// (CTA 0 only).
+// ---------------------------------------------------------------------------
+template <bool kFromQ>
+__global__ void __launch_bounds__(kEncWarps * 32, 1)
+k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
+    extern __shared__ __align__(1024) uint8_t encSmem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const RingCtrl rc = ring_ctrl(encSmem);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kEncStages; s++) {
+            mbar_init(rc.full + s, 1);
+            mbar_init(rc.empty + s, 1);
+        }
+        *rc.qHead = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        fence_proxy_async();
+    }
+    __syncthreads();
+    if (warp == 0) {
+        producer<kFromQ>(p, &tmap, encSmem, rc, lane);
+        return;
+    }
+    if (warp == kEncWarps - 1) {
+        if (blockIdx.x == 0) scan_blocks(p, lane);
+        return;
+    }
+    MinMaxAcc acc;
+    acc.f = acc.comp = -1;
+    acc.count = 0;
+    acc.lo = acc.hi = 0.0f;
+    acc.isPos = false;
+    acc.uw.tHi = acc.uw.tLo = acc.uw.L = 0.0f;
+    QuantCache qc;
+    qc.f = qc.comp = -1;
+    long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0;
+    const long long tStart = clock64();
+    while (true) {
+        const long long c0 = clock64();
+        uint32_t seq = 0;
+        if (lane == 0) seq = atomicAdd(rc.qHead, 1u);
+        seq = __shfl_sync(kFull, seq, 0);
+        const int s = (int)(seq % kEncStages);
+        mbar_wait(p.error, rc.full + s, (seq / kEncStages) & 1u, 5);
+        const WorkDesc d = rc.desc[s];
+        float *stage = reinterpret_cast<float *>(encSmem + kEncRingOff + s * kEncStageBytes);
+        const long long c1 = clock64();
+        tQueue += c1 - c0;
+        if (d.kind == kWorkStop) break;
+        if (d.kind == kWorkA) {
+            a_block(p, d, stage, acc, lane);
+            release_stage(rc, s, false, lane);
+            tA += clock64() - c1;
+            nA++;
+        } else if (d.kind == kWorkB) {
+            b_block<kFromQ>(p, d, stage, rc, s, qc, acc, lane);
+            tB += clock64() - c1;
+            nB++;
+        } else {
+            release_stage(rc, s, false, lane);
+        }
+    }
+    acc_flush(p, acc, lane);
+    if (p.stats && lane == 0) {
+        atomicAdd(p.stats + 0, (unsigned long long)tA);
+        atomicAdd(p.stats + 1, (unsigned long long)tB);
+        atomicAdd(p.stats + 4, (unsigned long long)tQueue);
+        atomicAdd(p.stats + 5, (unsigned long long)nA);
+        atomicAdd(p.stats + 6, (unsigned long long)nB);
+        atomicAdd(p.stats + 7, (unsigned long long)(clock64() - tStart));
+    }
+}
+
+// ---------------------------------------------------------------------------
+// k_finalize: one thread per field writes the 64-byte header and the field's
+// byte offset (the block tables were written at placement).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_finalize(EncodeParams p, int64_t fixedTotal) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f > p.nFields) return;
+    if (f == p.nFields) {
+        p.offsets[f] = (uint64_t)fixedTotal + (p.blkPrefix[p.nBlocks] & ~kPrefixReady) * 16;
+        return;
+    }
+    const DevField fd = p.fields[f];
+    const uint64_t p0 = p.blkPrefix[fd.firstBlock] & ~kPrefixReady;
+    const int64_t regionStart = fd.fixedBase + (int64_t)(p0 * 16);
+    p.offsets[f] = (uint64_t)regionStart;
+    if (regionStart + 64 + (int64_t)fd.nb * 48 > p.outCap) { atomicCAS(p.error, 0, kErrCapacity); return; }
+    const DevQuant qp = p.quant[f];
+    __align__(16) MnwDiffHeader h;
+    h.Magic = algo_Diff;
+    h.Version = MNWCUDA_ALGO_VERSION;
+    h.FieldCode = fd.fieldCode;
+    h.ParticleLen = fd.n;
+    h.Depth = (uint8_t)qp.depth;
+    h.Pad[0] = h.Pad[1] = h.Pad[2] = 0;
+    h.Width = fd.fieldCode == field_Posn ? fd.width : 0.0f;
+    for (int c = 0; c < 3; c++) { h.X0[c] = qp.X0[c]; h.X1[c] = qp.X1[c]; }
+    h.BlockLen = kBlockLen;
+    h.DitherRun = MNWCUDA_DITHER_RUN;
+    h.DitherLanes = MNWCUDA_DITHER_LANES;
+    h.DitherSeed = fd.seed;
+    const uint4 *src = reinterpret_cast<const uint4 *>(&h);
+    uint4 *dst = reinterpret_cast<uint4 *>(p.out + regionStart);
+    for (int i = 0; i < 4; i++) dst[i] = src[i];
+}
+
+}  // namespace mnw

@@ -1,0 +1,148 @@
+// enc_math.cuh -- the per-value arithmetic of the encoder: periodic unwrap as
+// thresholds, exact division-free quantisation, delta + width of one block.
+#pragma once
+
+#include "enc_common.cuh"
+
+namespace mnw {
+
+// ---------------------------------------------------------------------------
+// util_UndoPeriodic (src/util.c:106-110) tests rel = x - x[0] against +-L/2.
+// RN(x - anchor) is monotone in x, so each test is a threshold on x itself:
+// first_ge(anchor, c) = the smallest float v with RN(v - anchor) >= c.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float next_up(float x) {
+    uint32_t b = __float_as_uint(x);
+    if (x == 0.0f) return __uint_as_float(1u);
+    return __uint_as_float(x > 0.0f ? b + 1u : b - 1u);
+}
+__device__ __forceinline__ float next_down(float x) {
+    uint32_t b = __float_as_uint(x);
+    if (x == 0.0f) return __uint_as_float(0x80000001u);
+    return __uint_as_float(x > 0.0f ? b - 1u : b + 1u);
+}
+__device__ __forceinline__ float first_ge(float anchor, float c) {
+    float v = __fadd_rn(anchor, c);
+    for (int i = 0; i < 8; i++) {
+        float d = next_down(v);
+        if (__fsub_rn(d, anchor) >= c) v = d; else break;
+    }
+    for (int i = 0; i < 8; i++) {
+        if (!(__fsub_rn(v, anchor) >= c)) v = next_up(v); else break;
+    }
+    return v;
+}
+
+struct Unwrap {
+    float tHi, tLo, L;  // x >= tHi: x - L;  else x < tLo: x + L
+};
+__device__ __forceinline__ Unwrap make_unwrap(float anchor, float L) {
+    Unwrap u;
+    const float half = __fmul_rn(L, 0.5f);
+    u.tHi = first_ge(anchor, half);
+    u.tLo = first_ge(anchor, -half);
+    u.L = L;
+    return u;
+}
+__device__ __forceinline__ float unwrap_t(float v, const Unwrap &u) {
+    float r = v;
+    asm("{\n\t"
+        ".reg .pred up, dn;\n\t"
+        "setp.ge.f32 up, %1, %2;\n\t"
+        "setp.lt.and.f32 dn, %1, %3, !up;\n\t"
+        "@up sub.rn.f32 %0, %1, %4;\n\t"
+        "@dn add.rn.f32 %0, %1, %4;\n\t"
+        "}"
+        : "+f"(r) : "f"(v), "f"(u.tHi), "f"(u.tLo), "f"(u.L));
+    return r;
+}
+
+// util_UniformBinIndex (src/util.c:184-191) on 32 values per lane. See
+// bin_index_fast (minnow_kernels.cuh) for the division-free scaling. With
+// kBiased (depth <= 23) the truncation is an add in round-toward-zero mode:
+// for 0 <= s < 2^23, RZ(s + 2^23) = 2^23 + floor(s) exactly, i.e. the result's
+// bit pattern is kQBias + q; the bias cancels in the deltas. The clamp t >= 1
+// becomes fmin against the largest index (an integer, so trunc commutes).
+// s >= 0 always: x0 is the minimum of the very same unwrapped values.
+template <bool kPos, bool kBiased>
+__device__ __forceinline__ void quantise32(const float *stage, int lane, const Unwrap &uw, float x0,
+                                           double scale, uint32_t top, uint32_t (&q)[kChunk]) {
+    const float topf = (float)top;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const float4 e4 = reinterpret_cast<const float4 *>(stage)[swz_chunk(lane, j)];
+        float e[4] = {e4.x, e4.y, e4.z, e4.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            float u = e[i];
+            if (kPos) u = unwrap_t(u, uw);
+            const float a = __fsub_rn(u, x0);
+            const float s = __double2float_rn(__dmul_rn((double)a, scale));
+            if (kBiased) q[j * 4 + i] = __float_as_uint(__fadd_rz(fminf(s, topf), 8388608.0f));
+            else q[j * 4 + i] = min(__float2uint_rz(s), top);
+        }
+    }
+}
+
+struct BlockStats {
+    uint32_t first;
+    int dmin, w;
+};
+
+// delta along the block, min/max over j in [1, len), width; leaves the
+// residuals r[j] = d[j] - dmin in q (r[0] = 0, zeros beyond len)
+__device__ __forceinline__ BlockStats delta_width(uint32_t (&q)[kChunk], int len, int lane, int *error) {
+    const uint32_t prevLast = __shfl_up_sync(kFull, q[kChunk - 1], 1);
+    BlockStats bs;
+    bs.first = __shfl_sync(kFull, q[0], 0);
+    int dmin, dmax;
+    if (len == kBlockLen) {
+        const int d0 = (int)(q[0] - prevLast);
+        dmin = lane ? d0 : INT32_MAX;
+        dmax = lane ? d0 : INT32_MIN;
+#pragma unroll
+        for (int i = 1; i < kChunk; i++) {
+            const int d = (int)(q[i] - q[i - 1]);
+            dmin = min(dmin, d);
+            dmax = max(dmax, d);
+        }
+    } else {
+        dmin = INT32_MAX;
+        dmax = INT32_MIN;
+        uint32_t prev = prevLast;
+#pragma unroll
+        for (int i = 0; i < kChunk; i++) {
+            const int j = lane * kChunk + i;
+            const int d = (int)(q[i] - prev);
+            prev = q[i];
+            if (j >= 1 && j < len) { dmin = min(dmin, d); dmax = max(dmax, d); }
+        }
+    }
+    dmin = __reduce_min_sync(kFull, dmin);
+    dmax = __reduce_max_sync(kFull, dmax);
+    if (len <= 1) { dmin = 0; dmax = 0; }
+    int w = 32 - __clz((uint32_t)(dmax - dmin));
+    if (w > kMaxWidth) {  // only reachable with out-of-range integers at the CFunc boundary
+        if (lane == 0) atomicCAS(error, 0, kErrRange);
+        w = 0;
+    }
+    bs.dmin = dmin;
+    bs.w = w;
+    if (w > 0) {
+        if (len == kBlockLen) {
+#pragma unroll
+            for (int i = kChunk - 1; i >= 1; i--) q[i] = q[i] - q[i - 1] - (uint32_t)dmin;
+            q[0] = lane ? q[0] - prevLast - (uint32_t)dmin : 0u;
+        } else {
+#pragma unroll
+            for (int i = kChunk - 1; i >= 1; i--) {
+                const uint32_t r = q[i] - q[i - 1] - (uint32_t)dmin;
+                q[i] = (lane * kChunk + i < len) ? r : 0u;
+            }
+            q[0] = (lane && lane * kChunk < len) ? q[0] - prevLast - (uint32_t)dmin : 0u;
+        }
+    }
+    return bs;
+}
+
+}  // namespace mnw

@@ -1,0 +1,154 @@
+// enc_ring.cuh -- the input ring of k_encode. The producer warp of a CTA draws
+// group tickets; each of its 32 lanes owns one slot of the group: it works out
+// the slot's block, waits for the next ring stage to be free, writes the work
+// descriptor next to it and has the TMA unit copy the block's 4 KiB into the
+// stage (2D tensor map over the input as rows of 32 floats, 128-byte swizzle,
+// so that a consumer lane can read its 32 consecutive values without bank
+// conflicts). Consumer warps claim stages in order, wait on the stage's "full"
+// mbarrier and hand the stage back through its "empty" mbarrier.
+#pragma once
+
+#include "enc_common.cuh"
+
+namespace mnw {
+
+struct WorkDesc {  // 32 bytes, one per ring stage
+    int32_t kind;
+    int32_t f, comp, b;
+    int64_t blk;
+    int32_t len;
+    uint32_t slow;  // the block did not go through the TMA: the consumer loads it itself
+};
+
+struct RingCtrl {
+    uint64_t *full;   // [kEncStages] descriptor written and TMA bytes landed
+    uint64_t *empty;  // [kEncStages] the consumer is done with the stage
+    WorkDesc *desc;   // [kEncStages]
+    uint32_t *qHead;  // next stage sequence number to claim (consumers, atomic)
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t"
+                 ".reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.u32 %0, 1, 0, p;\n\t"
+                 "}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// bounded wait: a barrier that never completes raises kErrTimeout instead of hanging
+__device__ __forceinline__ void mbar_wait(int *error, uint64_t *bar, uint32_t parity, int site) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (kSpinLimit << 3)) { spin_timeout(error, site, -1); break; }
+    }
+}
+__device__ __forceinline__ void tma_load_block(void *smemDst, const CUtensorMap *map, int32_t row, uint64_t *bar,
+                                               uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%2, %3}], [%4], %5;" ::"r"(smem_u32(smemDst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(0), "r"(row), "r"(smem_u32(bar)), "l"(pol)
+        : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
+    RingCtrl rc;
+    uint8_t *c = smem + kEncCtrlOff;
+    rc.full = reinterpret_cast<uint64_t *>(c);
+    rc.empty = rc.full + kEncStages;
+    rc.desc = reinterpret_cast<WorkDesc *>(rc.empty + kEncStages);
+    rc.qHead = reinterpret_cast<uint32_t *>(rc.desc + kEncStages);
+    return rc;
+}
+
+// ---------------------------------------------------------------------------
+// producer warp: all 32 lanes, one slot each per pass
+// ---------------------------------------------------------------------------
+template <bool kFromQ>
+__device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMap *map, uint8_t *smem,
+                                         const RingCtrl &rc, int lane) {
+    const uint64_t keep = l2_policy_keep(), drop = l2_policy_drop();
+    const bool onlyB = kFromQ || p.lagG < 0;
+    uint32_t pass = 0;
+    uint32_t tk = 0;
+    if (lane == 0) tk = atomicAdd(p.ticket, 1u);
+    while (true) {
+        const int64_t g = (int64_t)__shfl_sync(kFull, tk, 0);
+        if (g >= p.nGroups) break;
+        if (lane == 0) tk = atomicAdd(p.ticket, 1u);  // the next ticket is on its way meanwhile
+        WorkDesc d;
+        d.kind = kWorkNop;
+        d.f = d.comp = d.b = 0;
+        d.len = 0;
+        d.slow = 1;
+        int64_t blk;
+        if (onlyB) {
+            blk = g * kGroupSlots + lane;
+            if (blk < p.nBlocks + p.lag2) d.kind = kWorkB;  // past the last block: placement only
+        } else if (lane < kGroupBlocks) {
+            blk = g * kGroupBlocks + lane;
+            if (blk < p.nBlocks) d.kind = kWorkA;
+        } else {
+            blk = (g - p.lagG) * kGroupBlocks + (lane - kGroupBlocks);
+            if (blk >= 0 && blk < p.nBlocks + p.lag2) d.kind = kWorkB;
+        }
+        d.blk = blk;
+        bool fast = false;
+        int64_t row = 0;
+        if (d.kind != kWorkNop && blk < p.nBlocks) {
+            locate_block(p, blk, d.f, d.comp, d.b);
+            const DevField *fdp = p.fields + d.f;
+            const int n = fdp->n;
+            d.len = min(kBlockLen, n - d.b * kBlockLen);
+            const int64_t off = fdp->ioOff + (int64_t)d.comp * n + (int64_t)d.b * kBlockLen;  // floats from p.in
+            row = (p.tmaShift + off) >> 5;
+            fast = !kFromQ && p.tmaShift >= 0 && d.len == kBlockLen && ((p.tmaShift + off) & 31) == 0 &&
+                   row + 32 <= p.tmaRows;
+            d.slow = fast ? 0u : 1u;
+        }
+        const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
+        const int s = (int)(seq % kEncStages);
+        const uint32_t use = seq / kEncStages;
+        if (use > 0) mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4);
+        rc.desc[s] = d;
+        if (fast) {
+            mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
+            tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
+                           d.kind == kWorkA ? keep : drop);
+        } else {
+            mbar_arrive(rc.full + s);
+        }
+        pass++;
+    }
+    if (lane < kEncConsumers) {  // one stop marker per consumer warp
+        const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
+        const int s = (int)(seq % kEncStages);
+        const uint32_t use = seq / kEncStages;
+        if (use > 0) mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4);
+        WorkDesc d;
+        d.kind = kWorkStop;
+        d.f = d.comp = d.b = 0;
+        d.blk = -1;
+        d.len = 0;
+        d.slow = 1;
+        rc.desc[s] = d;
+        mbar_arrive(rc.full + s);
+    }
+}
+
+}  // namespace mnw

@@ -3,6 +3,7 @@
 // decode_kernels.cuh / gen_kernels.cuh. sm_100a only; build with
 //   nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo -O3
 // There is no CPU path: without a device every entry point aborts.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cmath>
@@ -13,7 +14,7 @@
 
 #include "minnow_cuda.h"
 #include "decode_kernels.cuh"
-#include "encode_kernels.cuh"
+#include "enc_kernel.cuh"
 #include "gen_kernels.cuh"
 
 using namespace mnw;
@@ -65,8 +66,7 @@ struct MnwCudaCtx {
     int device = 0;
     int64_t launches = 0;
     uint64_t ditherSeed = 0;
-    Scratch fields, quant, minmax, tileState, tmp, seeds, tableOf, states, misc;
-    Scratch ring;
+    Scratch fields, quant, minmax, tileState, seeds, tableOf, states, misc, ring;
     Scratch ioA, ioB, ioC;  // host-buffer entry points: device staging
     uint64_t *jumpPow = nullptr;
     int *error = nullptr;     // device flag
@@ -74,10 +74,13 @@ struct MnwCudaCtx {
     cudaStream_t own = nullptr;  // stream of the synchronous host-buffer entry points
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     int smCount = 148;
-    int64_t encodeLag = -1;      // tiles between the A and B passes (-1: one field + margin)
-    int64_t encodeLag2 = 1024;   // tiles between parking a block (B) and placing it (C)
-    unsigned long long *debugStats = nullptr;  // MNWCUDA_DEBUG_STATS
-    int debugMask = 0;           // MNWCUDA_DEBUG_MASK: timing experiments, output bytes are wrong
+    int64_t encodeLag = -1;      // groups of 16 blocks between the A and B passes (-1: one field + encodeMargin)
+    int64_t encodeMargin = 384;  // groups of slack so that a field's parameters are ready when its B work starts
+    int64_t encodeLag2 = 8192;   // blocks between parking a packed block and placing it
+    void *encodeTiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime (no libcuda link)
+    unsigned long long *encStats = nullptr;  // MNWCUDA_ENCODE_STATS
+    EncodeParams lastEnc;        // most recent encode launch (diagnostics on a device-side timeout)
+    bool haveLastEnc = false;
     bool timing = false;         // mnwcuda_EnableKernelTiming
     cudaEvent_t ev[10] = {};     // encode: 0..2, decode: 5..8
     bool evSet[10] = {};
@@ -173,12 +176,20 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     ctx->ticket = reinterpret_cast<uint32_t *>(ctx->error) + 16;
     CUDA_CHECK(cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device));
     if (const char *e = getenv("MNWCUDA_ENCODE_LAG")) ctx->encodeLag = atoll(e);
-    if (const char *e = getenv("MNWCUDA_DEBUG_MASK")) ctx->debugMask = atoi(e);
-    if (getenv("MNWCUDA_DEBUG_STATS")) {
-        CUDA_CHECK(cudaMalloc(&ctx->debugStats, 64));
-        CUDA_CHECK(cudaMemset(ctx->debugStats, 0, 64));
+    if (const char *e = getenv("MNWCUDA_ENCODE_MARGIN")) ctx->encodeMargin = atoll(e) < 0 ? 0 : atoll(e);
+    if (const char *e = getenv("MNWCUDA_ENCODE_LAG2")) ctx->encodeLag2 = atoll(e) < 1024 ? 1024 : atoll(e);
+    {
+        cudaDriverEntryPointQueryResult qres;
+        CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ctx->encodeTiled, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !ctx->encodeTiled)
+            MNW_PANIC("cuTensorMapEncodeTiled is not available from this driver.");
     }
-    if (const char *e = getenv("MNWCUDA_ENCODE_LAG2")) ctx->encodeLag2 = atoll(e) < 128 ? 128 : atoll(e);
+    if (getenv("MNWCUDA_ENCODE_STATS")) {
+        CUDA_CHECK(cudaMalloc(&ctx->encStats, 64));
+        CUDA_CHECK(cudaMemset(ctx->encStats, 0, 64));
+    }
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -189,7 +200,7 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
-    Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->tmp, &ctx->seeds,
+    Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->seeds,
                       &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC};
     for (Scratch *s : all) s->release();
     cudaFree(ctx->jumpPow);
@@ -199,13 +210,15 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaStreamDestroy(ctx->copyOut);
     for (cudaEvent_t e : ctx->ev)
         if (e) cudaEventDestroy(e);
-    if (ctx->debugStats) {
-        unsigned long long h[4];
-        cudaMemcpy(h, ctx->debugStats, sizeof(h), cudaMemcpyDeviceToHost);
-        fprintf(stderr, "[mnwcuda look-back] tiles %llu rounds/tile %.2f polls/tile %.2f ns/tile %.0f\n", h[0],
-                (double)h[1] / (double)(h[0] ? h[0] : 1), (double)h[2] / (double)(h[0] ? h[0] : 1),
-                (double)h[3] / (double)(h[0] ? h[0] : 1));
-        cudaFree(ctx->debugStats);
+    if (ctx->encStats) {
+        unsigned long long h[8];
+        cudaMemcpy(h, ctx->encStats, sizeof(h), cudaMemcpyDeviceToHost);
+        const double tot = (double)h[7] > 0 ? (double)h[7] : 1.0;
+        fprintf(stderr, "[mnwcuda encode stats] consumer-time shares: A %.1f%% B %.1f%% queue %.1f%% | clk/A-block %.0f "
+                        "clk/B-block %.0f | blocks A %llu B %llu\n",
+                100.0 * h[0] / tot, 100.0 * h[1] / tot, 100.0 * h[4] / tot, (double)h[0] / (double)(h[5] ? h[5] : 1),
+                (double)h[1] / (double)(h[6] ? h[6] : 1), h[5], h[6]);
+        cudaFree(ctx->encStats);
     }
     delete ctx;
 }
@@ -244,6 +257,21 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
     CUDA_CHECK(cudaMemcpyAsync(&err, ctx->error, sizeof(int), cudaMemcpyDeviceToHost, s));
     CUDA_CHECK(cudaStreamSynchronize(s));
     if (err != 0) {
+        if (err == kErrTimeout) {
+            int info[4] = {0, 0, 0, 0};
+            CUDA_CHECK(cudaMemcpy(info, ctx->error, sizeof(info), cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[mnwcuda] device-side wait timed out: site %d, tile %d\n", info[1], info[2]);
+            if (ctx->haveLastEnc) {
+                const EncodeParams &q = ctx->lastEnc;
+                uint32_t st[4] = {0, 0, 0, 0};
+                cudaMemcpy(&st[0], q.ticket, 4, cudaMemcpyDeviceToHost);
+                cudaMemcpy(&st[1], q.aDone, 4, cudaMemcpyDeviceToHost);
+                cudaMemcpy(&st[2], q.ready, 4, cudaMemcpyDeviceToHost);
+                fprintf(stderr, "[mnwcuda] nBlocks %lld nGroups %lld lagG %lld lag2 %lld | ticket %u aDone[0] %u ready[0] %u\n",
+                        (long long)q.nBlocks, (long long)q.nGroups, (long long)q.lagG, (long long)q.lag2, st[0], st[1],
+                        st[2]);
+            }
+        }
         CUDA_CHECK(cudaMemsetAsync(ctx->error, 0, sizeof(int), s));
         CUDA_CHECK(cudaStreamSynchronize(s));
     }
@@ -259,7 +287,8 @@ struct Plan {
     std::vector<DevField> fields;
     int64_t nTiles = 0, nBlocks = 0, nTasks = 0, fixedTotal = 0, maxStreams = 0;
     int uniformTiles = 0, uniformBlocks = 0, uniformTasks = 0;
-    int64_t maxTilesPerField = 0;
+    int64_t maxTilesPerField = 0, maxBlocksPerField = 0;
+    int64_t floatEnd = 0;  // one past the last input float any field refers to
     bool hasEmpty = false;
 };
 
@@ -289,7 +318,9 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
         pl.nTiles += 3 * (int64_t)f.tilesPerComp;
         pl.nTasks += tasks;
         if (tasks * 32 > pl.maxStreams) pl.maxStreams = tasks * 32;
+        if (3 * (int64_t)f.nb > pl.maxBlocksPerField) pl.maxBlocksPerField = 3 * (int64_t)f.nb;
         if (3 * (int64_t)f.tilesPerComp > pl.maxTilesPerField) pl.maxTilesPerField = 3 * (int64_t)f.tilesPerComp;
+        if (d.Offset + 3ll * d.ParticleLen > pl.floatEnd) pl.floatEnd = d.Offset + 3ll * d.ParticleLen;
         if (d.ParticleLen == 0) pl.hasEmpty = true;
         if (d.ParticleLen != h[0].ParticleLen || d.ParticleLen == 0) uniform = false;
     }
@@ -298,7 +329,7 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
         pl.uniformBlocks = 3 * pl.fields[0].nb;
         pl.uniformTasks = (int)((3 * (int64_t)pl.fields[0].nb + kRun - 1) / kRun);
     }
-    if (pl.nTiles >= (1ll << 31) || pl.nTasks >= (1ll << 31)) return -5;
+    if (pl.nBlocks >= (1ll << 31) || pl.nTasks >= (1ll << 31)) return -5;
     return 0;
 }
 
@@ -309,41 +340,84 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     memset(&p, 0, sizeof(p));
     p.fields = static_cast<DevField *>(ctx->fields.need(nF * sizeof(DevField)));
     p.nFields = (int)nF;
-    p.uniformTiles = pl.uniformTiles;
+    p.uniformBlocks = pl.uniformBlocks;
     p.minmax = static_cast<uint32_t *>(ctx->minmax.need(nF * 6 * sizeof(uint32_t)));
     p.quant = static_cast<DevQuant *>(ctx->quant.need(nF * sizeof(DevQuant)));
-    // scratch ring for packed blocks waiting for their offset
+    // scratch ring for packed blocks waiting for their offset: a power of two > lag2
     p.lag2 = ctx->encodeLag2;
-    p.ringTiles = 1;
+    p.ringBlocks = 1;
     p.ringShift = 0;
-    while (p.ringTiles < pl.nTiles && p.ringTiles < 4 * p.lag2) { p.ringTiles <<= 1; p.ringShift++; }
-    p.scratch = static_cast<uint8_t *>(ctx->ring.need((size_t)p.ringTiles * kWarpsPerCta * kSlotBytes));
-    // one zeroed region: tile prefixes | tile sizes | ring counters | ticket | per-field A counters | ready flags
-    const size_t stateWords = (size_t)(pl.nTiles + 1) * 2 + (size_t)pl.nTiles + (size_t)p.ringTiles + 2 + 2 * nF;
-    p.tilePrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
-    p.tileAgg = reinterpret_cast<uint32_t *>(p.tilePrefix + pl.nTiles + 1);
-    p.slotDone = p.tileAgg + pl.nTiles;
-    p.ticket = p.slotDone + p.ringTiles;
+    while (p.ringBlocks < 2 * p.lag2) { p.ringBlocks <<= 1; p.ringShift++; }
+    uint8_t *ring = static_cast<uint8_t *>(
+        ctx->ring.need((size_t)p.ringBlocks * (kSlotWords * sizeof(uint32_t) + sizeof(BlockRec))));
+    p.scratch = reinterpret_cast<uint32_t *>(ring);
+    p.rec = reinterpret_cast<BlockRec *>(ring + (size_t)p.ringBlocks * kSlotWords * sizeof(uint32_t));
+    // one zeroed region: block prefixes | block sizes | slot counters | ticket | per-field A counters | ready flags
+    const size_t stateWords = (size_t)(pl.nBlocks + 1) * 2 + (size_t)pl.nBlocks + (size_t)p.ringBlocks + 2 + 2 * nF;
+    p.blkPrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
+    p.blkAgg = reinterpret_cast<uint32_t *>(p.blkPrefix + pl.nBlocks + 1);
+    p.slotDone = p.blkAgg + pl.nBlocks;
+    p.ticket = p.slotDone + p.ringBlocks;
     p.aDone = p.ticket + 2;
     p.ready = p.aDone + nF;
-    p.tmp = static_cast<TmpBlock *>(ctx->tmp.need((size_t)(pl.nBlocks + 1) * sizeof(TmpBlock)));
     p.out = d_out;
     p.outCap = outCap;
     p.offsets = d_offsets;
     p.error = ctx->error;
-    p.nTiles = pl.nTiles;
-    p.lag = -1;
+    p.nBlocks = pl.nBlocks;
+    p.lagG = -1;
     // pageable source: the copy is staged before the call returns
     CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), nF * sizeof(DevField),
                                cudaMemcpyHostToDevice, s));
-    CUDA_CHECK(cudaMemsetAsync(p.tilePrefix, 0, stateWords * sizeof(uint32_t), s));
+    CUDA_CHECK(cudaMemsetAsync(p.blkPrefix, 0, stateWords * sizeof(uint32_t), s));
     return p;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, bool fromQ, cudaStream_t s) {
+    EncodeParams q = p;
+    q.stats = ctx->encStats;
+    // the input as rows of 32 floats (128 bytes) from a 128-byte aligned base: one TMA box = 32 rows = one block
+    CUtensorMap map;
+    memset(&map, 0, sizeof(map));
+    q.tmaShift = -1;
+    q.tmaRows = 0;
+    if (!fromQ && p.in) {
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(p.in);
+        const uintptr_t base = addr & ~(uintptr_t)127;
+        const int64_t shift = (int64_t)((addr - base) / 4);
+        const int64_t rows = (shift + floatEnd) / 32;
+        if (rows >= 32 && rows < (1ll << 31)) {
+            cuuint64_t dims[2] = {32, (cuuint64_t)rows};
+            cuuint64_t strides[1] = {128};
+            cuuint32_t box[2] = {32, 32};
+            cuuint32_t elem[2] = {1, 1};
+            CUresult rc = reinterpret_cast<EncodeTiledFn>(ctx->encodeTiled)(
+                &map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, reinterpret_cast<void *>(base), dims, strides, box, elem,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (rc != CUDA_SUCCESS) MNW_PANIC("cuTensorMapEncodeTiled failed (%d).", (int)rc);
+            q.tmaShift = shift;
+            q.tmaRows = rows;
+        }
+    }
+    // one persistent CTA per SM; fewer when the batch is tiny
+    int64_t ctas = q.nGroups * kGroupSlots / kEncConsumers + 1;
+    if (ctas > ctx->smCount) ctas = ctx->smCount;
+    ctx->lastEnc = q;
+    ctx->haveLastEnc = true;
+    if (fromQ) k_encode<true><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
+    else k_encode<false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
+    ctx->launches++;
+    CUDA_CHECK(cudaGetLastError());
 }
 
 void launch_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParams &p, cudaStream_t s) {
     const int nF = (int)pl.fields.size();
-    int64_t threads = pl.nBlocks > nF + 1 ? pl.nBlocks : nF + 1;
-    k_finalize<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p, pl.nBlocks, pl.nTiles, pl.uniformBlocks);
+    k_finalize<<<(unsigned)((nF + 1 + 127) / 128), 128, 0, s>>>(p, pl.fixedTotal);
     ctx->launches++;
     CUDA_CHECK(cudaGetLastError());
 }
@@ -366,22 +440,20 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     if (rc) return rc;
     EncodeParams p = prepare_encode(ctx, pl, d_out, outCap, d_offsets, s);
     p.in = d_in;
-    // B(g) trails A(g) by one (largest) field plus the tiles that can be in flight
-    p.lag = ctx->encodeLag >= 0 ? ctx->encodeLag : pl.maxTilesPerField + 384;
-    if (p.lag < pl.maxTilesPerField) p.lag = pl.maxTilesPerField;
-    p.debugMask = ctx->debugMask;
-    p.debugStats = ctx->debugStats;
+    // the B work of a block trails its A work by one (largest) field plus what can be in flight
+    const int64_t fieldGroups = (pl.maxBlocksPerField + kGroupBlocks - 1) / kGroupBlocks;
+    p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + ctx->encodeMargin;
+    if (p.lagG < fieldGroups + 1) p.lagG = fieldGroups + 1;
     CUDA_CHECK(cudaMemsetAsync(p.minmax, 0xff, (size_t)nFields * 6 * sizeof(uint32_t), s));
     mark(ctx, 0, s);
     if (pl.hasEmpty) {
         k_depth_empty<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
         ctx->launches++;
     }
-    if (pl.nTiles > 0) {
-        p.nTickets = 2 * (pl.nTiles + p.lag + p.lag2);
-        if (p.nTickets >= (1ll << 31) - 1) return -5;
-        k_encode<false><<<(unsigned)(p.nTickets + 1), 256, 0, s>>>(p, nullptr);
-        ctx->launches++;
+    if (pl.nBlocks > 0) {
+        p.nGroups = (pl.nBlocks + p.lag2 + kGroupBlocks - 1) / kGroupBlocks + p.lagG;
+        if (p.nGroups >= (1ll << 31) - 1) return -5;
+        launch_encode(ctx, p, pl.floatEnd, false, s);
     }
     mark(ctx, 1, s);
     launch_finalize(ctx, pl, p, s);
@@ -468,6 +540,7 @@ void panic_on_status(MnwCudaCtx *ctx, cudaStream_t s, const char *what) {
     if (err == kErrCapacity) MNW_PANIC("%s: output capacity exceeded.", what);
     if (err == kErrPayload) MNW_PANIC("%s: malformed algo_Diff payload.", what);
     if (err == kErrRange) MNW_PANIC("%s: quantised values do not fit the declared depth.", what);
+    if (err == kErrTimeout) MNW_PANIC("%s: a device-side wait timed out (internal error).", what);
 }
 
 void *xmalloc(size_t bytes) {
@@ -707,10 +780,10 @@ extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
     if (inBytes) CUDA_CHECK(cudaMemcpyAsync(d_q, qf.Data, inBytes, cudaMemcpyHostToDevice, s));
     EncodeParams p = prepare_encode(ctx, pl, d_out, cap, d_off, s);
     CUDA_CHECK(cudaMemcpyAsync(p.quant, &dq, sizeof(dq), cudaMemcpyHostToDevice, s));
-    if (pl.nTiles > 0) {
-        p.nTickets = pl.nTiles + p.lag2;
-        k_encode<true><<<(unsigned)(p.nTickets + 1), 256, 0, s>>>(p, d_q);
-        ctx->launches++;
+    if (pl.nBlocks > 0) {
+        p.nGroups = (pl.nBlocks + p.lag2 + kGroupSlots - 1) / kGroupSlots;
+        p.qIn = d_q;
+        launch_encode(ctx, p, pl.floatEnd, true, s);
     }
     launch_finalize(ctx, pl, p, s);
     panic_on_status(ctx, s, "MnwCudaCompress_v0_9");

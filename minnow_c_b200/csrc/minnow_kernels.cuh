@@ -18,7 +18,7 @@ constexpr int kRun = MNWCUDA_DITHER_RUN;       // blocks per decode task
 constexpr int kMaxWidth = 25;                  // residual bits: |delta| < 2^24
 constexpr int kStageWords = 1024 + 32;         // per-warp staging: 1024 words + skew pads
 
-enum : int { kErrDepth = 1, kErrCapacity = 2, kErrPayload = 3, kErrRange = 4 };
+enum : int { kErrDepth = 1, kErrCapacity = 2, kErrPayload = 3, kErrRange = 4, kErrTimeout = 5 };
 
 // One field of the batch as the kernels see it (built on the host per call).
 struct DevField {

@@ -23,4 +23,9 @@ for code, data, delta, width in ((mc.FIELD_VELC, vel.reshape(-1), 1.0, 0.0), (mc
         n = min(got.size, want.size)
         bad = np.nonzero(got[:n] != want[:n])[0]
         print("first diffs", bad[:10], "count", bad.size, flush=True)
+        tg = _oracle.parse_table(got); tw = _oracle.parse_table(want)
+        for k in list(range(0, min(6, tg.size))) + list(range(max(0, tg.size - 3), tg.size)):
+            print(k, "got", tg[k], "want", tw[k], flush=True)
+        nbad = sum(1 for k in range(tg.size) if tg[k] != tw[k])
+        print("table entries differing:", nbad, "of", tg.size, flush=True)
 print("done", flush=True)
