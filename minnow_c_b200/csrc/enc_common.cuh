@@ -29,7 +29,9 @@ constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
 constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 32 + 16;
-constexpr int kEncSmemBytes = kEncCtrlOff + kEncCtrlBytes;
+constexpr int kEncFifoOff = kEncCtrlOff + kEncCtrlBytes;   // per consumer: records of its parked blocks
+constexpr int kEncFifoBytes = kEncConsumers * 8 * (16 + 8);
+constexpr int kEncSmemBytes = kEncFifoOff + kEncFifoBytes;
 constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bits x 1024, 16-byte padded
 
 constexpr uint32_t kAggReady = 0x80000000u;
@@ -58,12 +60,7 @@ struct EncodeParams {
     uint32_t *ticket;      // group ticket counter
     uint32_t *aDone;       // [nFields] A blocks finished
     uint32_t *ready;       // [nFields] quantisation parameters published
-    uint32_t *slotDone;    // [ringBlocks] placements out of the slot, cumulative
-    BlockRec *rec;         // [ringBlocks]
-    uint32_t *scratch;     // [ringBlocks][kSlotWords] packed blocks waiting for their offset
-    int64_t ringBlocks;    // a power of two > lag2
-    int ringShift;
-    int64_t lag2;          // block b is placed by whoever packs block b+lag2
+    uint32_t *scratch;     // [CTAs][kEncConsumers][kFifo][kSlotWords] packed blocks waiting for their offset
     int64_t tmaShift;      // floats between the tensor map's 128-byte aligned base and `in`; <0: no TMA
     int64_t tmaRows;       // rows of 32 floats covered by the tensor map
     uint8_t *out;

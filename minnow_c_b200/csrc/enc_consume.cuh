@@ -38,13 +38,16 @@ __device__ __forceinline__ void load_quant(const EncodeParams &p, const WorkDesc
     qc.top = 0;
     qc.biased = false;
     if (kFromQ) return;
-    if (p.lagG >= 0 && ld_acquire_u32(p.ready + d.f) == 0u) {
-        acc_flush(p, acc, lane);  // never wait while holding what others wait for
-        uint32_t spins = 0;
-        while (ld_acquire_u32(p.ready + d.f) == 0u) {
-            __nanosleep(100);
-            if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); break; }
+    if (p.lagG >= 0) {
+        if (ld_relaxed_u32(p.ready + d.f) == 0u) {
+            acc_flush(p, acc, lane);  // never wait while holding what others wait for
+            uint32_t spins = 0;
+            while (ld_relaxed_u32(p.ready + d.f) == 0u) {
+                __nanosleep(100);
+                if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); break; }
+            }
         }
+        __threadfence();  // acquire side of the flag: the parameters below were released before it
     }
     const DevQuant *qp = p.quant + d.f;  // written during this launch: read through L2
     qc.x0 = __ldcg(&qp->X0[d.comp]);
@@ -56,19 +59,34 @@ __device__ __forceinline__ void load_quant(const EncodeParams &p, const WorkDesc
 }
 
 // ---------------------------------------------------------------------------
-// placement of block `pl`: scratch slot -> final position, table entry
+// A consumer parks its packed blocks in scratch slots of its own (global memory,
+// L2 resident) and remembers them in a small FIFO; it places the oldest one as
+// soon as that block's prefix has arrived. The warp that wrote a slot is the one
+// that reads it back, lane for lane, so no fences are involved anywhere: the
+// size flags and the prefixes carry their own payload.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ void place_block(const EncodeParams &p, int64_t pl, uint64_t preW, MinMaxAcc &acc,
-                                            int lane) {
+constexpr int kFifo = 8;
+
+struct ParkFifo {
+    uint4 *rec;        // shared: [kFifo] first, minDelta, width, size16
+    int64_t *blk;      // shared: [kFifo]
+    uint32_t *slots;   // global: [kFifo][kSlotWords]
+    int head, count;
+};
+
+// copy the oldest parked block to its final position and write its table entry
+__device__ __forceinline__ void place_oldest(const EncodeParams &p, ParkFifo &ff, uint64_t preW, MinMaxAcc &acc,
+                                             int lane) {
+    const int k = ff.head;
+    const int64_t pl = ff.blk[k];
     if (!(preW & kPrefixReady)) {
-        acc_flush(p, acc, lane);
+        acc_flush(p, acc, lane);  // never wait while holding what others wait for
         uint32_t spins = 0;
         while (!((preW = ld_relaxed_u64(p.blkPrefix + pl)) & kPrefixReady)) {
             __nanosleep(200);
             if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); break; }
         }
     }
-    __threadfence();  // acquire: the block's record and scratch slot were released before its size
     const uint64_t pre = preW & ~kPrefixReady;
     int f, comp, b;
     locate_block(p, pl, f, comp, b);
@@ -78,45 +96,42 @@ __device__ __forceinline__ void place_block(const EncodeParams &p, int64_t pl, u
     for (uint32_t spins = 0; !(p0w & kPrefixReady) && spins < kSpinLimit; spins++)
         p0w = ld_relaxed_u64(p.blkPrefix + fdp->firstBlock);
     const uint64_t p0 = p0w & ~kPrefixReady;
-    const int64_t rp = pl & (p.ringBlocks - 1);
-    const uint4 rv = __ldcg(reinterpret_cast<const uint4 *>(p.rec + rp));
-    const uint32_t size16 = rv.w;
+    const uint4 rv = ff.rec[k];
+    const int size16 = (int)rv.w;
     const int64_t tableBase = fdp->fixedBase + (int64_t)(p0 * 16) + 64;
     const int64_t dstByte = tableBase + (int64_t)nb * 48 + (int64_t)((pre - p0) * 16);
     if (dstByte + (int64_t)size16 * 16 > p.outCap) {
         if (lane == 0) atomicCAS(p.error, 0, kErrCapacity);
     } else {
-        const uint4 *slot = reinterpret_cast<const uint4 *>(p.scratch + rp * kSlotWords);
+        const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)k * kSlotWords);
         uint4 *dst = reinterpret_cast<uint4 *>(p.out + dstByte);
-        for (int c = lane; c < (int)size16; c += 32) st_stream_u4(dst + c, __ldcg(slot + c));
+        for (int c = lane; c < size16; c += 64) {  // two chunks in flight per lane
+            const uint4 v0 = __ldcg(slot + c);
+            uint4 v1 = make_uint4(0u, 0u, 0u, 0u);
+            if (c + 32 < size16) v1 = __ldcg(slot + c + 32);
+            st_stream_u4(dst + c, v0);
+            if (c + 32 < size16) st_stream_u4(dst + c + 32, v1);
+        }
         if (lane == 0) {
             const uint4 e = make_uint4(rv.x, rv.y, rv.z, (uint32_t)(pre - p0));
             *reinterpret_cast<uint4 *>(p.out + tableBase + ((int64_t)comp * nb + b) * 16) = e;
         }
     }
     __syncwarp();
-    if (lane == 0) atomicAdd(p.slotDone + rp, 1u);
+    ff.head = (ff.head + 1) % kFifo;
+    ff.count--;
 }
 
 // ---------------------------------------------------------------------------
-// B work on block d.blk (blk >= nBlocks: placement only)
+// B work on block d.blk
 // ---------------------------------------------------------------------------
 template <bool kFromQ>
 __device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d, float *stage, const RingCtrl &rc,
-                                        int s, QuantCache &qc, MinMaxAcc &acc, int lane) {
+                                        int s, QuantCache &qc, MinMaxAcc &acc, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
-    const int64_t pl = blk - p.lag2;
-    // loads whose results are needed late go out first
+    // the oldest parked block's prefix is needed late: ask for it first
     uint64_t preW = 0;
-    if (pl >= 0) preW = ld_relaxed_u64(p.blkPrefix + pl);
-    if (blk >= p.nBlocks) {
-        release_stage(rc, s, false, lane);
-        if (pl >= 0 && pl < p.nBlocks) place_block(p, pl, preW, acc, lane);
-        return;
-    }
-    const int64_t ringPos = blk & (p.ringBlocks - 1);
-    const uint32_t tenants = (uint32_t)(blk >> p.ringShift);  // earlier users of the scratch slot
-    uint32_t freed = ld_acquire_u32(p.slotDone + ringPos);
+    if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
     load_quant<kFromQ>(p, d, qc, acc, lane);
 
     const int len = d.len;
@@ -157,21 +172,22 @@ __device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d
     if (!kFromQ && qc.biased) bs.first -= kQBias;
     const int nWords = (len * bs.w + 31) >> 5;
     const uint32_t size16 = (uint32_t)((nWords + 3) >> 2);
+    // the size is all the scan warp needs: publish it before anything else
+    if (lane == 0)
+        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.blkAgg + blk), "r"(kAggReady | size16) : "memory");
 
     // pack through the block's own stage (its values are in registers by now)
     uint32_t *tmp = reinterpret_cast<uint32_t *>(stage);
     __syncwarp();
     if (bs.w > 0) pack_dispatch(bs.w, q, tmp, lane);
     __syncwarp();
-    if (freed < tenants) {  // the slot's previous tenant has not been placed yet (rare)
-        acc_flush(p, acc, lane);
-        uint32_t spins = 0;
-        while ((freed = ld_acquire_u32(p.slotDone + ringPos)) < tenants) {
-            __nanosleep(200);
-            if (++spins > kSpinLimit) { spin_timeout(p.error, 8, blk); break; }
-        }
+    if (ff.count == kFifo) {  // no free slot: the oldest block has to go now
+        place_oldest(p, ff, preW, acc, lane);
+        preW = 0;
+        if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
     }
-    uint4 *slot = reinterpret_cast<uint4 *>(p.scratch + ringPos * kSlotWords);
+    const int k = (ff.head + ff.count) % kFifo;
+    uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
     for (int c = lane; c < (int)size16; c += 32) {
         const int m = c * 4;
         uint4 o;
@@ -181,14 +197,19 @@ __device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d
         o.w = m + 3 < nWords ? tmp[skew(m + 3)] : 0u;
         slot[c] = o;
     }
-    if (lane == 0)
-        *reinterpret_cast<uint4 *>(p.rec + ringPos) = make_uint4(bs.first, (uint32_t)bs.dmin, (uint32_t)bs.w, size16);
-    release_stage(rc, s, true, lane);  // includes __syncwarp: every lane's slot stores precede lane 0's release
     if (lane == 0) {
-        __threadfence();
-        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.blkAgg + blk), "r"(kAggReady | size16) : "memory");
+        ff.rec[k] = make_uint4(bs.first, (uint32_t)bs.dmin, (uint32_t)bs.w, size16);
+        ff.blk[k] = blk;
     }
-    if (pl >= 0) place_block(p, pl, preW, acc, lane);
+    ff.count++;
+    release_stage(rc, s, true, lane);  // includes __syncwarp
+    // place whatever has its prefix already (normally exactly one block per block packed)
+    while (ff.count > 0 && (preW & kPrefixReady)) {
+        place_oldest(p, ff, preW, acc, lane);
+        preW = 0;
+        if (ff.count > 1) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
+        else break;
+    }
 }
 
 }  // namespace mnw

@@ -41,6 +41,12 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     acc.uw.tHi = acc.uw.tLo = acc.uw.L = 0.0f;
     QuantCache qc;
     qc.f = qc.comp = -1;
+    const int c = warp - 1;
+    ParkFifo ff;
+    ff.rec = reinterpret_cast<uint4 *>(encSmem + kEncFifoOff) + c * kFifo;
+    ff.blk = reinterpret_cast<int64_t *>(encSmem + kEncFifoOff + kEncConsumers * kFifo * 16) + c * kFifo;
+    ff.slots = p.scratch + ((size_t)blockIdx.x * kEncConsumers + c) * kFifo * kSlotWords;
+    ff.head = ff.count = 0;
     long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0;
     const long long tStart = clock64();
     while (true) {
@@ -61,7 +67,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             tA += clock64() - c1;
             nA++;
         } else if (d.kind == kWorkB) {
-            b_block<kFromQ>(p, d, stage, rc, s, qc, acc, lane);
+            b_block<kFromQ>(p, d, stage, rc, s, qc, acc, ff, lane);
             tB += clock64() - c1;
             nB++;
         } else {
@@ -69,6 +75,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         }
     }
     acc_flush(p, acc, lane);
+    while (ff.count > 0) place_oldest(p, ff, 0, acc, lane);
     if (p.stats && lane == 0) {
         atomicAdd(p.stats + 0, (unsigned long long)tA);
         atomicAdd(p.stats + 1, (unsigned long long)tB);

@@ -9,13 +9,12 @@
 //            deltaToDepth (src/quant.c:186-196, 684-693) and publishes the
 //            field's quantisation parameters.
 //   B work   util_UniformBinIndex + delta + width + util_U32UniformPack of one
-//            block (src/util.c:173-196, 311-355). The packed words are written
-//            through the block's own ring stage into a scratch slot in global
-//            memory (L2 resident) and the size is published.
+//            block (src/util.c:173-196, 311-355). The size is published at once;
+//            the packed words go through the block's own ring stage into one of
+//            the consumer's scratch slots in global memory (L2 resident).
 //   scan     one warp turns the sizes into exclusive prefixes, in block order.
-//   place    the consumer that packs block b also copies block b-lag2, whose
-//            prefix has long arrived, from its scratch slot to its final
-//            position and writes its table entry.
+//   place    a few blocks later the same consumer copies the block from its
+//            slot to its final position and writes its table entry.
 // Work only ever waits for work with a smaller ticket, and every waiting warp
 // has flushed what others may wait for, so the waits cannot deadlock.
 #pragma once
@@ -71,10 +70,9 @@ __global__ void k_depth_empty(EncodeParams p) {
 }
 
 // ---------------------------------------------------------------------------
-// Scan warp: block sizes -> exclusive prefixes, 1024 blocks per poll. A size is
-// published with release semantics after the block's scratch slot and record;
-// the acquire polls here and the release stores of the prefixes pass that on
-// to whoever places the block.
+// Scan warp: block sizes -> exclusive prefixes, 1024 blocks per poll. The flag
+// words carry their own payload and nobody reads anything else through them,
+// so relaxed accesses are enough.
 // ---------------------------------------------------------------------------
 constexpr int kScanPerLane = 32;
 
@@ -100,7 +98,6 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
             for (int k = 0; k < kScanPerLane; k++)
                 if (!(a[k] & kAggReady)) a[k] = ld_relaxed_u32(p.blkAgg + mine + k);
         }
-        __threadfence();  // acquire side of the sizes seen above; the prefixes below are released
         uint32_t local = 0;
 #pragma unroll
         for (int k = 0; k < kScanPerLane; k++) local += a[k] & ~kAggReady;
@@ -121,7 +118,6 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
         }
         running += __shfl_sync(kFull, incl, 31);
     }
-    __threadfence();
     if (lane == 0) st_release_u64(p.blkPrefix + p.nBlocks, kPrefixReady | running);
 }
 

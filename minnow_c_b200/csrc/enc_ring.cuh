@@ -99,18 +99,18 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         int64_t blk;
         if (onlyB) {
             blk = g * kGroupSlots + lane;
-            if (blk < p.nBlocks + p.lag2) d.kind = kWorkB;  // past the last block: placement only
+            if (blk < p.nBlocks) d.kind = kWorkB;
         } else if (lane < kGroupBlocks) {
             blk = g * kGroupBlocks + lane;
             if (blk < p.nBlocks) d.kind = kWorkA;
         } else {
             blk = (g - p.lagG) * kGroupBlocks + (lane - kGroupBlocks);
-            if (blk >= 0 && blk < p.nBlocks + p.lag2) d.kind = kWorkB;
+            if (blk >= 0 && blk < p.nBlocks) d.kind = kWorkB;
         }
         d.blk = blk;
         bool fast = false;
         int64_t row = 0;
-        if (d.kind != kWorkNop && blk < p.nBlocks) {
+        if (d.kind != kWorkNop) {
             locate_block(p, blk, d.f, d.comp, d.b);
             const DevField *fdp = p.fields + d.f;
             const int n = fdp->n;

@@ -76,7 +76,6 @@ struct MnwCudaCtx {
     int smCount = 148;
     int64_t encodeLag = -1;      // groups of 16 blocks between the A and B passes (-1: one field + encodeMargin)
     int64_t encodeMargin = 384;  // groups of slack so that a field's parameters are ready when its B work starts
-    int64_t encodeLag2 = 8192;   // blocks between parking a packed block and placing it
     void *encodeTiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime (no libcuda link)
     unsigned long long *encStats = nullptr;  // MNWCUDA_ENCODE_STATS
     EncodeParams lastEnc;        // most recent encode launch (diagnostics on a device-side timeout)
@@ -177,7 +176,6 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     CUDA_CHECK(cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device));
     if (const char *e = getenv("MNWCUDA_ENCODE_LAG")) ctx->encodeLag = atoll(e);
     if (const char *e = getenv("MNWCUDA_ENCODE_MARGIN")) ctx->encodeMargin = atoll(e) < 0 ? 0 : atoll(e);
-    if (const char *e = getenv("MNWCUDA_ENCODE_LAG2")) ctx->encodeLag2 = atoll(e) < 1024 ? 1024 : atoll(e);
     {
         cudaDriverEntryPointQueryResult qres;
         CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ctx->encodeTiled, cudaEnableDefault, &qres));
@@ -267,9 +265,8 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
                 cudaMemcpy(&st[0], q.ticket, 4, cudaMemcpyDeviceToHost);
                 cudaMemcpy(&st[1], q.aDone, 4, cudaMemcpyDeviceToHost);
                 cudaMemcpy(&st[2], q.ready, 4, cudaMemcpyDeviceToHost);
-                fprintf(stderr, "[mnwcuda] nBlocks %lld nGroups %lld lagG %lld lag2 %lld | ticket %u aDone[0] %u ready[0] %u\n",
-                        (long long)q.nBlocks, (long long)q.nGroups, (long long)q.lagG, (long long)q.lag2, st[0], st[1],
-                        st[2]);
+                fprintf(stderr, "[mnwcuda] nBlocks %lld nGroups %lld lagG %lld | ticket %u aDone[0] %u ready[0] %u\n",
+                        (long long)q.nBlocks, (long long)q.nGroups, (long long)q.lagG, st[0], st[1], st[2]);
             }
         }
         CUDA_CHECK(cudaMemsetAsync(ctx->error, 0, sizeof(int), s));
@@ -343,21 +340,14 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     p.uniformBlocks = pl.uniformBlocks;
     p.minmax = static_cast<uint32_t *>(ctx->minmax.need(nF * 6 * sizeof(uint32_t)));
     p.quant = static_cast<DevQuant *>(ctx->quant.need(nF * sizeof(DevQuant)));
-    // scratch ring for packed blocks waiting for their offset: a power of two > lag2
-    p.lag2 = ctx->encodeLag2;
-    p.ringBlocks = 1;
-    p.ringShift = 0;
-    while (p.ringBlocks < 2 * p.lag2) { p.ringBlocks <<= 1; p.ringShift++; }
-    uint8_t *ring = static_cast<uint8_t *>(
-        ctx->ring.need((size_t)p.ringBlocks * (kSlotWords * sizeof(uint32_t) + sizeof(BlockRec))));
-    p.scratch = reinterpret_cast<uint32_t *>(ring);
-    p.rec = reinterpret_cast<BlockRec *>(ring + (size_t)p.ringBlocks * kSlotWords * sizeof(uint32_t));
-    // one zeroed region: block prefixes | block sizes | slot counters | ticket | per-field A counters | ready flags
-    const size_t stateWords = (size_t)(pl.nBlocks + 1) * 2 + (size_t)pl.nBlocks + (size_t)p.ringBlocks + 2 + 2 * nF;
+    // per-consumer scratch slots for packed blocks waiting for their offset
+    p.scratch = static_cast<uint32_t *>(
+        ctx->ring.need((size_t)ctx->smCount * kEncConsumers * kFifo * kSlotWords * sizeof(uint32_t)));
+    // one zeroed region: block prefixes | block sizes | ticket | per-field A counters | ready flags
+    const size_t stateWords = (size_t)(pl.nBlocks + 1) * 2 + (size_t)pl.nBlocks + 2 + 2 * nF;
     p.blkPrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
     p.blkAgg = reinterpret_cast<uint32_t *>(p.blkPrefix + pl.nBlocks + 1);
-    p.slotDone = p.blkAgg + pl.nBlocks;
-    p.ticket = p.slotDone + p.ringBlocks;
+    p.ticket = p.blkAgg + pl.nBlocks;
     p.aDone = p.ticket + 2;
     p.ready = p.aDone + nF;
     p.out = d_out;
@@ -451,7 +441,7 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
         ctx->launches++;
     }
     if (pl.nBlocks > 0) {
-        p.nGroups = (pl.nBlocks + p.lag2 + kGroupBlocks - 1) / kGroupBlocks + p.lagG;
+        p.nGroups = (pl.nBlocks + kGroupBlocks - 1) / kGroupBlocks + p.lagG;
         if (p.nGroups >= (1ll << 31) - 1) return -5;
         launch_encode(ctx, p, pl.floatEnd, false, s);
     }
@@ -781,7 +771,7 @@ extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
     EncodeParams p = prepare_encode(ctx, pl, d_out, cap, d_off, s);
     CUDA_CHECK(cudaMemcpyAsync(p.quant, &dq, sizeof(dq), cudaMemcpyHostToDevice, s));
     if (pl.nBlocks > 0) {
-        p.nGroups = (pl.nBlocks + p.lag2 + kGroupSlots - 1) / kGroupSlots;
+        p.nGroups = (pl.nBlocks + kGroupSlots - 1) / kGroupSlots;
         p.qIn = d_q;
         launch_encode(ctx, p, pl.floatEnd, true, s);
     }
