@@ -9,7 +9,10 @@
 // (unwrap + min/max) of blocks 16g..16g+15, slots 16..31 the B work (quantise +
 // delta + width + pack) of blocks 16(g-lagG)..16(g-lagG)+15 -- lagG groups
 // later, when the field's parameters are known and, with luck, the block is
-// still in L2.
+// still in L2. Everything that crosses warps goes through self-validating
+// words (a value plus a "there" bit, zero-initialised, relaxed accesses): block
+// min/max -> the reduce warp -> per-component parameters; block sizes -> the
+// scan warp -> block prefixes. No fences on the data path.
 #pragma once
 
 #include <cuda.h>
@@ -28,7 +31,7 @@ constexpr int kGroupSlots = 32;      // slots per ticket
 constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
-constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 32 + 16;
+constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 32 + 16 + kEncStages * 4;
 constexpr int kEncFifoOff = kEncCtrlOff + kEncCtrlBytes;   // per consumer: records of its parked blocks
 constexpr int kEncFifoBytes = kEncConsumers * 8 * (16 + 8);
 constexpr int kEncSmemBytes = kEncFifoOff + kEncFifoBytes;
@@ -36,6 +39,7 @@ constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bit
 
 constexpr uint32_t kAggReady = 0x80000000u;
 constexpr uint64_t kPrefixReady = 1ull << 63;
+constexpr uint64_t kFqValid = 1ull << 63;
 constexpr uint32_t kQBias = 0x4b000000u;  // bit pattern of 2^23: trunc by add.rz keeps it in the exponent
 
 enum : int { kWorkNop = 0, kWorkA = 1, kWorkB = 2, kWorkStop = 3 };
@@ -58,8 +62,8 @@ struct EncodeParams {
     uint32_t *blkAgg;      // [nBlocks] kAggReady | packed size of the block, 16-byte units
     uint64_t *blkPrefix;   // [nBlocks+1] kPrefixReady | exclusive prefix, written by the scan warp
     uint32_t *ticket;      // group ticket counter
-    uint32_t *aDone;       // [nFields] A blocks finished
-    uint32_t *ready;       // [nFields] quantisation parameters published
+    uint64_t *blkMM;       // [nBlocks] ord(min) | ~ord(max) << 32 of the block, 0 = not there yet
+    uint64_t *fq;          // [nFields][3][2] published parameters of a component (see publish_quant)
     uint32_t *scratch;     // [CTAs][kEncConsumers][kFifo][kSlotWords] packed blocks waiting for their offset
     int64_t tmaShift;      // floats between the tensor map's 128-byte aligned base and `in`; <0: no TMA
     int64_t tmaRows;       // rows of 32 floats covered by the tensor map
@@ -70,6 +74,7 @@ struct EncodeParams {
     int64_t nBlocks;
     int64_t nGroups;       // tickets >= nGroups mean "no more work"
     int64_t lagG;          // B of group g-lagG rides with A of group g; <0: no A work (quant given)
+    int dbg;               // MNWCUDA_DBG: debugging switches
     unsigned long long *stats;  // MNWCUDA_ENCODE_STATS: per-phase clock totals over all warps, or null
 };
 

@@ -10,6 +10,7 @@ __device__ __forceinline__ void release_stage(const RingCtrl &rc, int s, bool wr
     __syncwarp();
     if (lane == 0) {
         if (wrote) fence_proxy_async();  // generic-proxy writes before the TMA's next fill
+        rc.uses[s] = rc.uses[s] + 1;     // one owner at a time
         mbar_arrive(rc.empty + s);
     }
 }
@@ -25,9 +26,8 @@ struct QuantCache {
 };
 
 template <bool kFromQ>
-__device__ __forceinline__ void load_quant(const EncodeParams &p, const WorkDesc &d, QuantCache &qc, MinMaxAcc &acc,
-                                           int lane) {
-    if (qc.f == d.f && qc.comp == d.comp) return;
+__device__ __forceinline__ bool load_quant(const EncodeParams &p, const WorkDesc &d, QuantCache &qc, int lane) {
+    if (qc.f == d.f && qc.comp == d.comp) return true;
     const DevField *fdp = p.fields + d.f;
     qc.f = d.f;
     qc.comp = d.comp;
@@ -37,25 +37,32 @@ __device__ __forceinline__ void load_quant(const EncodeParams &p, const WorkDesc
     qc.scale = 0.0;
     qc.top = 0;
     qc.biased = false;
-    if (kFromQ) return;
+    if (kFromQ) return true;
+    uint32_t depth;
     if (p.lagG >= 0) {
-        if (ld_relaxed_u32(p.ready + d.f) == 0u) {
-            acc_flush(p, acc, lane);  // never wait while holding what others wait for
-            uint32_t spins = 0;
-            while (ld_relaxed_u32(p.ready + d.f) == 0u) {
-                __nanosleep(100);
-                if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); break; }
-            }
+        // published during this launch by the reduce warp
+        const uint64_t *w = p.fq + ((int64_t)d.f * 3 + d.comp) * 2;
+        uint64_t w0 = ld_relaxed_u64(w), w1 = ld_relaxed_u64(w + 1);
+        uint32_t spins = 0;
+        while (!(w0 & w1 & kFqValid)) {
+            __nanosleep(100);
+            if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); qc.f = -1; return false; }
+            w0 = ld_relaxed_u64(w);
+            w1 = ld_relaxed_u64(w + 1);
         }
-        __threadfence();  // acquire side of the flag: the parameters below were released before it
+        qc.scale = __longlong_as_double((long long)(w0 & ~kFqValid));
+        qc.x0 = __uint_as_float((uint32_t)w1);
+        depth = (uint32_t)(w1 >> 32) & 0xffu;
+    } else {
+        const DevQuant *qp = p.quant + d.f;  // given by the caller, written before the launch
+        qc.x0 = __ldg(&qp->X0[d.comp]);
+        qc.scale = __ldg(&qp->scale);
+        depth = __ldg(&qp->depth);
     }
-    const DevQuant *qp = p.quant + d.f;  // written during this launch: read through L2
-    qc.x0 = __ldcg(&qp->X0[d.comp]);
-    qc.scale = __ldcg(&qp->scale);
-    const uint32_t depth = __ldcg(&qp->depth);
     qc.top = (1u << depth) - 1u;
     qc.biased = depth <= 23;
     if (qc.isPos) qc.uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * fdp->n), fdp->width);
+    return true;
 }
 
 // ---------------------------------------------------------------------------
@@ -75,16 +82,14 @@ struct ParkFifo {
 };
 
 // copy the oldest parked block to its final position and write its table entry
-__device__ __forceinline__ void place_oldest(const EncodeParams &p, ParkFifo &ff, uint64_t preW, MinMaxAcc &acc,
-                                             int lane) {
+__device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff, uint64_t preW, int lane) {
     const int k = ff.head;
     const int64_t pl = ff.blk[k];
     if (!(preW & kPrefixReady)) {
-        acc_flush(p, acc, lane);  // never wait while holding what others wait for
         uint32_t spins = 0;
         while (!((preW = ld_relaxed_u64(p.blkPrefix + pl)) & kPrefixReady)) {
             __nanosleep(200);
-            if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); break; }
+            if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); return false; }
         }
     }
     const uint64_t pre = preW & ~kPrefixReady;
@@ -120,19 +125,21 @@ __device__ __forceinline__ void place_oldest(const EncodeParams &p, ParkFifo &ff
     __syncwarp();
     ff.head = (ff.head + 1) % kFifo;
     ff.count--;
+    return true;
 }
 
 // ---------------------------------------------------------------------------
 // B work on block d.blk
 // ---------------------------------------------------------------------------
+// (false: a wait timed out, the caller leaves the kernel)
 template <bool kFromQ>
-__device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d, float *stage, const RingCtrl &rc,
-                                        int s, QuantCache &qc, MinMaxAcc &acc, ParkFifo &ff, int lane) {
+__device__ __forceinline__ bool b_block(const EncodeParams &p, const WorkDesc &d, float *stage, const RingCtrl &rc,
+                                        int s, QuantCache &qc, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
     // the oldest parked block's prefix is needed late: ask for it first
     uint64_t preW = 0;
     if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
-    load_quant<kFromQ>(p, d, qc, acc, lane);
+    if (!load_quant<kFromQ>(p, d, qc, lane)) return false;
 
     const int len = d.len;
     uint32_t q[kChunk];
@@ -182,7 +189,7 @@ __device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d
     if (bs.w > 0) pack_dispatch(bs.w, q, tmp, lane);
     __syncwarp();
     if (ff.count == kFifo) {  // no free slot: the oldest block has to go now
-        place_oldest(p, ff, preW, acc, lane);
+        if (!place_oldest(p, ff, preW, lane)) return false;
         preW = 0;
         if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
     }
@@ -205,11 +212,11 @@ __device__ __forceinline__ void b_block(const EncodeParams &p, const WorkDesc &d
     release_stage(rc, s, true, lane);  // includes __syncwarp
     // place whatever has its prefix already (normally exactly one block per block packed)
     while (ff.count > 0 && (preW & kPrefixReady)) {
-        place_oldest(p, ff, preW, acc, lane);
+        if (!place_oldest(p, ff, preW, lane)) return false;
         preW = 0;
-        if (ff.count > 1) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
-        else break;
+        if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
     }
+    return true;
 }
 
 }  // namespace mnw

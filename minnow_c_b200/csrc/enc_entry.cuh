@@ -7,7 +7,7 @@ namespace mnw {
 
 // ---------------------------------------------------------------------------
 // k_encode: warp 0 = producer, warps 1..14 = consumers, warp 15 = the scan warp
-// (CTA 0 only).
+// in CTA 0 and the reduce warp in CTA 1 (the host launches at least two CTAs).
 // ---------------------------------------------------------------------------
 template <bool kFromQ>
 __global__ void __launch_bounds__(kEncWarps * 32, 1)
@@ -21,6 +21,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             mbar_init(rc.empty + s, 1);
         }
         *rc.qHead = 0;
+        for (int s = 0; s < kEncStages; s++) rc.uses[s] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_proxy_async();
     }
@@ -31,14 +32,13 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     }
     if (warp == kEncWarps - 1) {
         if (blockIdx.x == 0) scan_blocks(p, lane);
+        else if (blockIdx.x == 1 && p.lagG >= 0 && !kFromQ) reduce_fields(p, lane);
         return;
     }
-    MinMaxAcc acc;
-    acc.f = acc.comp = -1;
-    acc.count = 0;
-    acc.lo = acc.hi = 0.0f;
-    acc.isPos = false;
-    acc.uw.tHi = acc.uw.tLo = acc.uw.L = 0.0f;
+    UnwrapCache uc;
+    uc.f = uc.comp = -1;
+    uc.isPos = false;
+    uc.uw.tHi = uc.uw.tLo = uc.uw.L = 0.0f;
     QuantCache qc;
     qc.f = qc.comp = -1;
     const int c = warp - 1;
@@ -47,6 +47,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     ff.blk = reinterpret_cast<int64_t *>(encSmem + kEncFifoOff + kEncConsumers * kFifo * 16) + c * kFifo;
     ff.slots = p.scratch + ((size_t)blockIdx.x * kEncConsumers + c) * kFifo * kSlotWords;
     ff.head = ff.count = 0;
+    bool drain = false;
     long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0;
     const long long tStart = clock64();
     while (true) {
@@ -55,27 +56,39 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         if (lane == 0) seq = atomicAdd(rc.qHead, 1u);
         seq = __shfl_sync(kFull, seq, 0);
         const int s = (int)(seq % kEncStages);
-        mbar_wait(p.error, rc.full + s, (seq / kEncStages) & 1u, 5);
+        const uint32_t use = seq / kEncStages;
+        for (uint32_t spins = 0; rc.uses[s] < use;) {
+            if (++spins > (kSpinLimit << 6)) { spin_timeout(p.error, 7, -1); return; }
+        }
+        if (!mbar_wait(p.error, rc.full + s, use & 1u, 5)) return;
         const WorkDesc d = rc.desc[s];
         float *stage = reinterpret_cast<float *>(encSmem + kEncRingOff + s * kEncStageBytes);
         const long long c1 = clock64();
         tQueue += c1 - c0;
         if (d.kind == kWorkStop) break;
+        if (drain) {  // after a timeout: hand the stages back untouched so that the kernel can end
+            release_stage(rc, s, false, lane);
+            continue;
+        }
         if (d.kind == kWorkA) {
-            a_block(p, d, stage, acc, lane);
+            a_block(p, d, stage, uc, lane);
             release_stage(rc, s, false, lane);
             tA += clock64() - c1;
             nA++;
         } else if (d.kind == kWorkB) {
-            b_block<kFromQ>(p, d, stage, rc, s, qc, acc, ff, lane);
+            if (!b_block<kFromQ>(p, d, stage, rc, s, qc, ff, lane)) {
+                drain = true;
+                release_stage(rc, s, false, lane);
+                continue;
+            }
             tB += clock64() - c1;
             nB++;
         } else {
             release_stage(rc, s, false, lane);
         }
     }
-    acc_flush(p, acc, lane);
-    while (ff.count > 0) place_oldest(p, ff, 0, acc, lane);
+    while (ff.count > 0 && !drain)
+        if (!place_oldest(p, ff, 0, lane)) return;
     if (p.stats && lane == 0) {
         atomicAdd(p.stats + 0, (unsigned long long)tA);
         atomicAdd(p.stats + 1, (unsigned long long)tB);

@@ -2,12 +2,11 @@
 // 14 consumer warps, and the scan warp in CTA 0) and k_finalize.
 //
 //   A work   util_UndoPeriodic + util_MinMax of one block (src/util.c:97-113,
-//            27-46) straight out of the ring; a consumer keeps the running
-//            min/max of consecutive blocks of one component in registers and
-//            flushes them with two atomics when the component changes -- and
-//            before it ever waits for anything. Whoever completes a field runs
-//            deltaToDepth (src/quant.c:186-196, 684-693) and publishes the
-//            field's quantisation parameters.
+//            27-46) straight out of the ring; the block's min/max go out as
+//            one 64-bit word.
+//   reduce   one warp (CTA 1) folds the blocks' min/max in block order; at the
+//            end of a field it runs deltaToDepth (src/quant.c:186-196, 684-693)
+//            and publishes the field's quantisation parameters.
 //   B work   util_UniformBinIndex + delta + width + util_U32UniformPack of one
 //            block (src/util.c:173-196, 311-355). The size is published at once;
 //            the packed words go through the block's own ring stage into one of
@@ -15,8 +14,9 @@
 //   scan     one warp turns the sizes into exclusive prefixes, in block order.
 //   place    a few blocks later the same consumer copies the block from its
 //            slot to its final position and writes its table entry.
-// Work only ever waits for work with a smaller ticket, and every waiting warp
-// has flushed what others may wait for, so the waits cannot deadlock.
+// A work never waits; B work waits for A work with smaller tickets only (through
+// the reduce warp); placement waits for B work of smaller blocks only (through
+// the scan warp): the waits cannot deadlock.
 #pragma once
 
 #include "enc_math.cuh"
@@ -60,6 +60,17 @@ __device__ __forceinline__ void compute_quant(const EncodeParams &p, int f) {
     // both clamps and converts to 0 on the host; scale 0 gives the same zeros
     q.scale = md > 0.0f ? __ddiv_rn((double)(1u << depth), (double)md) : 0.0;
     p.quant[f] = q;
+    // what B work needs, as two self-validating words per component: the scale
+    // (a non-negative double: its sign bit is free) and X0 | depth << 32
+    if (p.fq) {
+        for (int c = 0; c < 3; c++) {
+            uint64_t *w = p.fq + ((int64_t)f * 3 + c) * 2;
+            const uint64_t w0 = kFqValid | (uint64_t)__double_as_longlong(q.scale);
+            const uint64_t w1 = kFqValid | ((uint64_t)depth << 32) | (uint64_t)__float_as_uint(q.X0[c]);
+            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(w), "l"(w0) : "memory");
+            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(w + 1), "l"(w1) : "memory");
+        }
+    }
 }
 
 // one thread per field: empty fields have no blocks to trigger compute_quant
@@ -122,36 +133,107 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
 }
 
 // ---------------------------------------------------------------------------
-// A work: running min/max of one component in registers
+// Reduce warp: block min/max -> per-component min/max -> the field's
+// parameters, in block order, 512 blocks per poll. All lanes walk the
+// (field, component) sequence together.
 // ---------------------------------------------------------------------------
-struct MinMaxAcc {
-    int f, comp;      // -1: nothing pending
-    uint32_t count;   // blocks folded in
-    float lo, hi;
+constexpr int kRedPerLane = 16;
+
+struct RedWalk {
+    int f, comp;
+    int64_t compEnd;  // global index one past the component's last block
+    uint32_t lo, hi;  // running ord(min), ~ord(max)
+};
+
+__device__ __forceinline__ void red_skip_empty(const EncodeParams &p, RedWalk &w) {
+    while (w.f < p.nFields && p.fields[w.f].nb == 0) w.f++;  // k_depth_empty took care of those
+    if (w.f < p.nFields) w.compEnd = p.fields[w.f].firstBlock + p.fields[w.f].nb;
+}
+
+__device__ __forceinline__ void red_finish_comp(const EncodeParams &p, RedWalk &w, int lane) {
+    if (lane == 0) {
+        uint32_t *mm = p.minmax + ((int64_t)w.f * 3 + w.comp) * 2;
+        mm[0] = w.lo;
+        mm[1] = w.hi;
+        if (w.comp == 2) compute_quant(p, w.f);  // reads back what this thread has just written
+    }
+    w.lo = w.hi = 0xffffffffu;
+    if (++w.comp == 3) {
+        w.comp = 0;
+        w.f++;
+        red_skip_empty(p, w);
+    } else {
+        w.compEnd += p.fields[w.f].nb;
+    }
+}
+
+__device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
+    RedWalk w;
+    w.f = w.comp = 0;
+    w.compEnd = 0;
+    w.lo = w.hi = 0xffffffffu;
+    red_skip_empty(p, w);
+    constexpr int kWin = 32 * kRedPerLane;
+    for (int64_t base = 0; base < p.nBlocks; base += kWin) {
+        uint64_t a[kRedPerLane];
+#pragma unroll
+        for (int k = 0; k < kRedPerLane; k++) {
+            const int64_t blk = base + k * 32 + lane;
+            a[k] = blk < p.nBlocks ? ld_relaxed_u64(p.blkMM + blk) : ~0ull;
+        }
+        uint32_t spins = 0;
+        while (true) {
+            bool all = true;
+#pragma unroll
+            for (int k = 0; k < kRedPerLane; k++) all = all && a[k] != 0ull;
+            if (__all_sync(kFull, all)) break;
+            if (++spins > kSpinLimit) {
+                if (lane == 0) spin_timeout(p.error, 6, base);
+                return;
+            }
+            if (spins > 16) __nanosleep(100);
+#pragma unroll
+            for (int k = 0; k < kRedPerLane; k++)
+                if (a[k] == 0ull) a[k] = ld_relaxed_u64(p.blkMM + base + k * 32 + lane);
+        }
+        if (base + kWin <= w.compEnd && !(p.dbg & 1)) {
+            // the whole window lies in one component
+            uint32_t lo = 0xffffffffu, hi = 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < kRedPerLane; k++) {
+                lo = min(lo, (uint32_t)a[k]);
+                hi = min(hi, (uint32_t)(a[k] >> 32));
+            }
+            w.lo = min(w.lo, __reduce_min_sync(kFull, lo));
+            w.hi = min(w.hi, __reduce_min_sync(kFull, hi));
+            if (base + kWin == w.compEnd) red_finish_comp(p, w, lane);
+        } else {
+#pragma unroll
+            for (int k = 0; k < kRedPerLane; k++) {
+                int64_t s0 = base + k * 32;
+                const int64_t s1 = min(s0 + 32, p.nBlocks);
+                const int64_t blk = s0 + lane;
+                while (s0 < s1) {
+                    const int64_t e = min(s1, w.compEnd);
+                    const bool in = blk >= s0 && blk < e;
+                    w.lo = min(w.lo, __reduce_min_sync(kFull, in ? (uint32_t)a[k] : 0xffffffffu));
+                    w.hi = min(w.hi, __reduce_min_sync(kFull, in ? (uint32_t)(a[k] >> 32) : 0xffffffffu));
+                    s0 = e;
+                    if (s0 == w.compEnd) red_finish_comp(p, w, lane);
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// A work: min/max of one block
+// ---------------------------------------------------------------------------
+struct UnwrapCache {  // of the component a consumer last did A work on
+    int f, comp;      // -1: empty
     Unwrap uw;
     bool isPos;
 };
-
-__device__ __forceinline__ void acc_flush(const EncodeParams &p, MinMaxAcc &acc, int lane) {
-    if (acc.f < 0) return;
-    const uint32_t olo = __reduce_min_sync(kFull, ord_from_float(acc.lo));
-    const uint32_t ohi = __reduce_min_sync(kFull, ~ord_from_float(acc.hi));  // max kept inverted (0xff memset)
-    if (lane == 0) {
-        uint32_t *mm = p.minmax + ((int64_t)acc.f * 3 + acc.comp) * 2;
-        atomicMin(mm, olo);
-        atomicMin(mm + 1, ohi);
-        __threadfence();
-        const uint32_t done = atomicAdd(p.aDone + acc.f, acc.count);
-        if (done + acc.count == 3u * (uint32_t)p.fields[acc.f].nb) {
-            __threadfence();
-            compute_quant(p, acc.f);
-            __threadfence();
-            st_release_u32(p.ready + acc.f, 1u);
-        }
-    }
-    acc.f = -1;
-    acc.count = 0;
-}
 
 template <bool kPos>
 __device__ __forceinline__ void minmax_stage(const float4 *st, int lane, const Unwrap &uw, float &lo, float &hi) {
@@ -170,34 +252,36 @@ __device__ __forceinline__ void minmax_stage(const float4 *st, int lane, const U
     }
 }
 
-__device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d, const float *stage, MinMaxAcc &acc,
+__device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d, const float *stage, UnwrapCache &uc,
                                         int lane) {
-    if (acc.f != d.f || acc.comp != d.comp) {
-        acc_flush(p, acc, lane);
+    if (uc.f != d.f || uc.comp != d.comp) {
         const DevField *fdp = p.fields + d.f;
-        acc.f = d.f;
-        acc.comp = d.comp;
-        acc.lo = __int_as_float(0x7f800000);
-        acc.hi = __int_as_float(0xff800000);
-        acc.isPos = fdp->fieldCode == field_Posn;
-        acc.uw.tHi = acc.uw.tLo = acc.uw.L = 0.0f;
-        if (acc.isPos) acc.uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * fdp->n), fdp->width);
+        uc.f = d.f;
+        uc.comp = d.comp;
+        uc.isPos = fdp->fieldCode == field_Posn;
+        uc.uw.tHi = uc.uw.tLo = uc.uw.L = 0.0f;
+        if (uc.isPos) uc.uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * fdp->n), fdp->width);
     }
+    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
     if (!d.slow) {
         const float4 *st = reinterpret_cast<const float4 *>(stage);
-        if (acc.isPos) minmax_stage<true>(st, lane, acc.uw, acc.lo, acc.hi);
-        else minmax_stage<false>(st, lane, acc.uw, acc.lo, acc.hi);
+        if (uc.isPos) minmax_stage<true>(st, lane, uc.uw, lo, hi);
+        else minmax_stage<false>(st, lane, uc.uw, lo, hi);
     } else {
         const DevField *fdp = p.fields + d.f;
         const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
         for (int i = lane; i < d.len; i += 32) {
             float u = __ldg(src + i);
-            if (acc.isPos) u = unwrap_t(u, acc.uw);
-            acc.lo = fminf(acc.lo, u);
-            acc.hi = fmaxf(acc.hi, u);
+            if (uc.isPos) u = unwrap_t(u, uc.uw);
+            lo = fminf(lo, u);
+            hi = fmaxf(hi, u);
         }
     }
-    acc.count++;
+    const uint32_t olo = __reduce_min_sync(kFull, ord_from_float(lo));
+    const uint32_t ohi = __reduce_min_sync(kFull, ~ord_from_float(hi));  // max kept inverted: one min for both
+    if (lane == 0)
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p.blkMM + d.blk),
+                     "l"((uint64_t)olo | ((uint64_t)ohi << 32)) : "memory");
 }
 
 }  // namespace mnw

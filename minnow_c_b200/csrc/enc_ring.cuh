@@ -5,7 +5,11 @@
 // stage (2D tensor map over the input as rows of 32 floats, 128-byte swizzle,
 // so that a consumer lane can read its 32 consecutive values without bank
 // conflicts). Consumer warps claim stages in order, wait on the stage's "full"
-// mbarrier and hand the stage back through its "empty" mbarrier.
+// mbarrier and hand the stage back through its "empty" mbarrier. A parity wait
+// can only tell the current phase from the one before, and consumers racing
+// through no-op slots can claim the next use of a stage whose current fill is
+// still in flight: so a consumer first waits until the stage's previous use has
+// been handed back (a plain counter), and only then for the fill.
 #pragma once
 
 #include "enc_common.cuh"
@@ -25,6 +29,7 @@ struct RingCtrl {
     uint64_t *empty;  // [kEncStages] the consumer is done with the stage
     WorkDesc *desc;   // [kEncStages]
     uint32_t *qHead;  // next stage sequence number to claim (consumers, atomic)
+    volatile uint32_t *uses;  // [kEncStages] how many times the stage has been handed back
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -50,11 +55,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
     return ok != 0;
 }
 // bounded wait: a barrier that never completes raises kErrTimeout instead of hanging
-__device__ __forceinline__ void mbar_wait(int *error, uint64_t *bar, uint32_t parity, int site) {
+// (false: the caller leaves the kernel, it must not touch the ring again)
+__device__ __forceinline__ bool mbar_wait(int *error, uint64_t *bar, uint32_t parity, int site) {
     uint32_t spins = 0;
+    unsigned long long t0 = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (kSpinLimit << 3)) { spin_timeout(error, site, -1); break; }
+        if ((++spins & 1023u) == 0) {  // a try_wait may itself suspend the warp for a while: bound the time
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > 1000000000ull) { spin_timeout(error, site, -1); return false; }
+        }
     }
+    return true;
 }
 __device__ __forceinline__ void tma_load_block(void *smemDst, const CUtensorMap *map, int32_t row, uint64_t *bar,
                                                uint64_t pol) {
@@ -73,6 +86,7 @@ __device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
     rc.empty = rc.full + kEncStages;
     rc.desc = reinterpret_cast<WorkDesc *>(rc.empty + kEncStages);
     rc.qHead = reinterpret_cast<uint32_t *>(rc.desc + kEncStages);
+    rc.uses = rc.qHead + 4;
     return rc;
 }
 
@@ -124,7 +138,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
-        if (use > 0) mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4);
+        if (use > 0 && !mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4)) return;
         rc.desc[s] = d;
         if (fast) {
             mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
@@ -139,7 +153,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
-        if (use > 0) mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4);
+        if (use > 0 && !mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4)) return;
         WorkDesc d;
         d.kind = kWorkStop;
         d.f = d.comp = d.b = 0;

@@ -263,10 +263,24 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
                 const EncodeParams &q = ctx->lastEnc;
                 uint32_t st[4] = {0, 0, 0, 0};
                 cudaMemcpy(&st[0], q.ticket, 4, cudaMemcpyDeviceToHost);
-                cudaMemcpy(&st[1], q.aDone, 4, cudaMemcpyDeviceToHost);
-                cudaMemcpy(&st[2], q.ready, 4, cudaMemcpyDeviceToHost);
-                fprintf(stderr, "[mnwcuda] nBlocks %lld nGroups %lld lagG %lld | ticket %u aDone[0] %u ready[0] %u\n",
-                        (long long)q.nBlocks, (long long)q.nGroups, (long long)q.lagG, st[0], st[1], st[2]);
+                fprintf(stderr, "[mnwcuda] nBlocks %lld nGroups %lld lagG %lld | ticket %u\n", (long long)q.nBlocks,
+                        (long long)q.nGroups, (long long)q.lagG, st[0]);
+                // first block without a prefix / a size / a min-max, first component without parameters
+                const size_t nb = (size_t)q.nBlocks;
+                std::vector<uint64_t> pre(nb + 1), mm(nb), fq((size_t)q.nFields * 6);
+                std::vector<uint32_t> agg(nb);
+                cudaMemcpy(pre.data(), q.blkPrefix, (nb + 1) * 8, cudaMemcpyDeviceToHost);
+                cudaMemcpy(mm.data(), q.blkMM, nb * 8, cudaMemcpyDeviceToHost);
+                cudaMemcpy(agg.data(), q.blkAgg, nb * 4, cudaMemcpyDeviceToHost);
+                cudaMemcpy(fq.data(), q.fq, fq.size() * 8, cudaMemcpyDeviceToHost);
+                size_t iPre = 0, iAgg = 0, iMM = 0, iFq = 0, nAggMissing = 0;
+                while (iPre <= nb && (pre[iPre] >> 63)) iPre++;
+                while (iAgg < nb && (agg[iAgg] >> 31)) iAgg++;
+                for (size_t i = 0; i < nb; i++) nAggMissing += !(agg[i] >> 31);
+                while (iMM < nb && mm[iMM]) iMM++;
+                while (iFq < fq.size() && (fq[iFq] >> 63)) iFq++;
+                fprintf(stderr, "[mnwcuda] first missing: prefix %zu size %zu (missing in all %zu) minmax %zu params word %zu of %zu\n",
+                        iPre, iAgg, nAggMissing, iMM, iFq, fq.size());
             }
         }
         CUDA_CHECK(cudaMemsetAsync(ctx->error, 0, sizeof(int), s));
@@ -343,13 +357,13 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     // per-consumer scratch slots for packed blocks waiting for their offset
     p.scratch = static_cast<uint32_t *>(
         ctx->ring.need((size_t)ctx->smCount * kEncConsumers * kFifo * kSlotWords * sizeof(uint32_t)));
-    // one zeroed region: block prefixes | block sizes | ticket | per-field A counters | ready flags
-    const size_t stateWords = (size_t)(pl.nBlocks + 1) * 2 + (size_t)pl.nBlocks + 2 + 2 * nF;
+    // one zeroed region: block prefixes | block min/max | component parameters | block sizes | ticket
+    const size_t stateWords = (size_t)(pl.nBlocks + 1) * 2 + (size_t)pl.nBlocks * 2 + 12 * nF + (size_t)pl.nBlocks + 2;
     p.blkPrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
-    p.blkAgg = reinterpret_cast<uint32_t *>(p.blkPrefix + pl.nBlocks + 1);
+    p.blkMM = p.blkPrefix + pl.nBlocks + 1;
+    p.fq = p.blkMM + pl.nBlocks;
+    p.blkAgg = reinterpret_cast<uint32_t *>(p.fq + 6 * nF);
     p.ticket = p.blkAgg + pl.nBlocks;
-    p.aDone = p.ticket + 2;
-    p.ready = p.aDone + nF;
     p.out = d_out;
     p.outCap = outCap;
     p.offsets = d_offsets;
@@ -370,6 +384,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
 void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, bool fromQ, cudaStream_t s) {
     EncodeParams q = p;
     q.stats = ctx->encStats;
+    if (const char *e = getenv("MNWCUDA_DBG")) q.dbg = atoi(e);
     // the input as rows of 32 floats (128 bytes) from a 128-byte aligned base: one TMA box = 32 rows = one block
     CUtensorMap map;
     memset(&map, 0, sizeof(map));
@@ -397,6 +412,7 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     // one persistent CTA per SM; fewer when the batch is tiny
     int64_t ctas = q.nGroups * kGroupSlots / kEncConsumers + 1;
     if (ctas > ctx->smCount) ctas = ctx->smCount;
+    if (ctas < 2) ctas = 2;  // the reduce warp lives in CTA 1
     ctx->lastEnc = q;
     ctx->haveLastEnc = true;
     if (fromQ) k_encode<true><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
@@ -434,7 +450,6 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     const int64_t fieldGroups = (pl.maxBlocksPerField + kGroupBlocks - 1) / kGroupBlocks;
     p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + ctx->encodeMargin;
     if (p.lagG < fieldGroups + 1) p.lagG = fieldGroups + 1;
-    CUDA_CHECK(cudaMemsetAsync(p.minmax, 0xff, (size_t)nFields * 6 * sizeof(uint32_t), s));
     mark(ctx, 0, s);
     if (pl.hasEmpty) {
         k_depth_empty<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
