@@ -31,14 +31,18 @@ constexpr int kGroupSlots = 32;      // slots per ticket
 constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
-constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 32 + 16 + kEncStages * 4;
+constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 64 + 16 + kEncStages * 4;
 constexpr int kEncFifoOff = kEncCtrlOff + kEncCtrlBytes;   // per consumer: records of its parked blocks
 constexpr int kEncFifoBytes = kEncConsumers * 8 * (16 + 8);
-constexpr int kEncSmemBytes = kEncFifoOff + kEncFifoBytes;
+constexpr int kEncStatOff = kEncFifoOff + kEncFifoBytes;   // per consumer: 8 phase clocks (MNWCUDA_ENCODE_STATS)
+constexpr int kEncSmemBytes = kEncStatOff + kEncConsumers * 64;
 constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bits x 1024, 16-byte padded
 
-constexpr uint32_t kAggReady = 0x80000000u;
-constexpr uint64_t kPrefixReady = 1ull << 63;
+constexpr uint32_t kAggReady = 0x8000u;       // in a 16-bit size word
+constexpr uint32_t kRelReady = 0x80000000u;   // in a 32-bit window-relative prefix
+constexpr uint64_t kPrefixReady = 1ull << 63; // in a 64-bit window base
+constexpr int kScanWin = 1024;                // blocks per scan window
+constexpr int kRedWin = 512;                  // blocks per reduce window
 constexpr uint64_t kFqValid = 1ull << 63;
 constexpr uint32_t kQBias = 0x4b000000u;  // bit pattern of 2^23: trunc by add.rz keeps it in the exponent
 
@@ -59,10 +63,11 @@ struct EncodeParams {
     int uniformBlocks;     // >0: every field has this many blocks (fast lookup)
     uint32_t *minmax;      // [nFields][3][2] ordered-uint min, ~max
     DevQuant *quant;       // [nFields]
-    uint32_t *blkAgg;      // [nBlocks] kAggReady | packed size of the block, 16-byte units
-    uint64_t *blkPrefix;   // [nBlocks+1] kPrefixReady | exclusive prefix, written by the scan warp
+    uint16_t *blkAgg;      // [nBlocks, padded to kScanWin] kAggReady | packed size of the block, 16-byte units
+    uint32_t *blkRel;      // [nBlocks, padded] kRelReady | exclusive prefix within the block's scan window
+    uint64_t *winBase;     // [nWin+1] kPrefixReady | exclusive prefix at the window's start; [nWin] = total
     uint32_t *ticket;      // group ticket counter
-    uint64_t *blkMM;       // [nBlocks] ord(min) | ~ord(max) << 32 of the block, 0 = not there yet
+    uint64_t *blkMM;       // [nBlocks, padded to kRedWin] ord(min) | ~ord(max) << 32 of the block, 0 = not there yet
     uint64_t *fq;          // [nFields][3][2] published parameters of a component (see publish_quant)
     uint32_t *scratch;     // [CTAs][kEncConsumers][kFifo][kSlotWords] packed blocks waiting for their offset
     int64_t tmaShift;      // floats between the tensor map's 128-byte aligned base and `in`; <0: no TMA
@@ -104,6 +109,25 @@ __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *p) {
 }
 __device__ __forceinline__ void st_release_u64(uint64_t *p, uint64_t v) {
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ld_relaxed_u4(const void *p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u4(void *p, uint4 v) {
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+// exclusive prefix (16-byte units) of block `blk`, if the scan has got there
+__device__ __forceinline__ bool block_prefix(const uint32_t *blkRel, const uint64_t *winBase, int64_t blk,
+                                             uint64_t &pre) {
+    uint32_t rel;
+    uint64_t wb;  // two independent loads: one round trip
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(rel) : "l"(blkRel + blk) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(wb) : "l"(winBase + blk / kScanWin) : "memory");
+    pre = (wb & ~kPrefixReady) + (rel & ~kRelReady);
+    return (rel & kRelReady) && (wb & kPrefixReady);
 }
 __device__ __forceinline__ uint64_t l2_policy_keep() {
     uint64_t pol;

@@ -15,53 +15,20 @@ __device__ __forceinline__ void release_stage(const RingCtrl &rc, int s, bool wr
     }
 }
 
-// quantisation parameters of the component a consumer is working on
-struct QuantCache {
-    int f, comp;  // -1: empty
-    float x0;
-    double scale;
-    uint32_t top;
-    bool biased, isPos;
-    Unwrap uw;
-};
-
-template <bool kFromQ>
-__device__ __forceinline__ bool load_quant(const EncodeParams &p, const WorkDesc &d, QuantCache &qc, int lane) {
-    if (qc.f == d.f && qc.comp == d.comp) return true;
-    const DevField *fdp = p.fields + d.f;
-    qc.f = d.f;
-    qc.comp = d.comp;
-    qc.isPos = fdp->fieldCode == field_Posn;
-    qc.uw.tHi = qc.uw.tLo = qc.uw.L = 0.0f;
-    qc.x0 = 0.0f;
-    qc.scale = 0.0;
-    qc.top = 0;
-    qc.biased = false;
-    if (kFromQ) return true;
-    uint32_t depth;
-    if (p.lagG >= 0) {
-        // published during this launch by the reduce warp
-        const uint64_t *w = p.fq + ((int64_t)d.f * 3 + d.comp) * 2;
-        uint64_t w0 = ld_relaxed_u64(w), w1 = ld_relaxed_u64(w + 1);
-        uint32_t spins = 0;
-        while (!(w0 & w1 & kFqValid)) {
-            __nanosleep(100);
-            if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); qc.f = -1; return false; }
-            w0 = ld_relaxed_u64(w);
-            w1 = ld_relaxed_u64(w + 1);
-        }
-        qc.scale = __longlong_as_double((long long)(w0 & ~kFqValid));
-        qc.x0 = __uint_as_float((uint32_t)w1);
-        depth = (uint32_t)(w1 >> 32) & 0xffu;
-    } else {
-        const DevQuant *qp = p.quant + d.f;  // given by the caller, written before the launch
-        qc.x0 = __ldg(&qp->X0[d.comp]);
-        qc.scale = __ldg(&qp->scale);
-        depth = __ldg(&qp->depth);
+// the producer found the component's parameters not yet published: wait for them here
+__device__ __forceinline__ bool wait_quant(const EncodeParams &p, WorkDesc &d) {
+    const uint64_t *w = p.fq + ((int64_t)d.f * 3 + d.comp) * 2;
+    uint64_t w0 = ld_relaxed_u64(w), w1 = ld_relaxed_u64(w + 1);
+    uint32_t spins = 0;
+    while (!(w0 & w1 & kFqValid)) {
+        __nanosleep(100);
+        if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); return false; }
+        w0 = ld_relaxed_u64(w);
+        w1 = ld_relaxed_u64(w + 1);
     }
-    qc.top = (1u << depth) - 1u;
-    qc.biased = depth <= 23;
-    if (qc.isPos) qc.uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * fdp->n), fdp->width);
+    d.scale = __longlong_as_double((long long)(w0 & ~kFqValid));
+    d.x0 = __uint_as_float((uint32_t)w1);
+    d.depth = (uint32_t)(w1 >> 32) & 0xffu;
     return true;
 }
 
@@ -79,28 +46,47 @@ struct ParkFifo {
     int64_t *blk;      // shared: [kFifo]
     uint32_t *slots;   // global: [kFifo][kSlotWords]
     int head, count;
+    int p0Field;       // field whose first-block prefix is cached in p0, or -1
+    uint64_t p0;
+    unsigned long long *wst;  // shared: phase clocks of this warp, or null
 };
+
+#define MNW_PHASE(i)                                   \
+    if (ff.wst) {                                      \
+        const long long tNow_ = clock64();             \
+        if (lane == 0) ff.wst[i] += tNow_ - tPh;       \
+        tPh = tNow_;                                   \
+    }
+
+// kPrefixReady | prefix of the block, or 0 if the scan has not got there yet
+__device__ __forceinline__ uint64_t peek_prefix(const EncodeParams &p, int64_t blk) {
+    uint64_t pre;
+    return block_prefix(p.blkRel, p.winBase, blk, pre) ? (kPrefixReady | pre) : 0ull;
+}
 
 // copy the oldest parked block to its final position and write its table entry
 __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff, uint64_t preW, int lane) {
     const int k = ff.head;
     const int64_t pl = ff.blk[k];
+    uint64_t pre = preW & ~kPrefixReady;
     if (!(preW & kPrefixReady)) {
         uint32_t spins = 0;
-        while (!((preW = ld_relaxed_u64(p.blkPrefix + pl)) & kPrefixReady)) {
+        while (!block_prefix(p.blkRel, p.winBase, pl, pre)) {
             __nanosleep(200);
             if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); return false; }
         }
     }
-    const uint64_t pre = preW & ~kPrefixReady;
     int f, comp, b;
     locate_block(p, pl, f, comp, b);
     const DevField *fdp = p.fields + f;
     const int nb = fdp->nb;
-    uint64_t p0w = ld_relaxed_u64(p.blkPrefix + fdp->firstBlock);  // published no later than `pre`, bar reordering
-    for (uint32_t spins = 0; !(p0w & kPrefixReady) && spins < kSpinLimit; spins++)
-        p0w = ld_relaxed_u64(p.blkPrefix + fdp->firstBlock);
-    const uint64_t p0 = p0w & ~kPrefixReady;
+    if (ff.p0Field != f) {  // published no later than `pre`, bar reordering
+        uint64_t p0 = 0;
+        for (uint32_t spins = 0; !block_prefix(p.blkRel, p.winBase, fdp->firstBlock, p0) && spins < kSpinLimit; spins++) {}
+        ff.p0 = p0;
+        ff.p0Field = f;
+    }
+    const uint64_t p0 = ff.p0;
     const uint4 rv = ff.rec[k];
     const int size16 = (int)rv.w;
     const int64_t tableBase = fdp->fixedBase + (int64_t)(p0 * 16) + 64;
@@ -133,13 +119,17 @@ __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff
 // ---------------------------------------------------------------------------
 // (false: a wait timed out, the caller leaves the kernel)
 template <bool kFromQ>
-__device__ __forceinline__ bool b_block(const EncodeParams &p, const WorkDesc &d, float *stage, const RingCtrl &rc,
-                                        int s, QuantCache &qc, ParkFifo &ff, int lane) {
+__device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, float *stage, const RingCtrl &rc,
+                                        int s, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
     // the oldest parked block's prefix is needed late: ask for it first
     uint64_t preW = 0;
-    if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
-    if (!load_quant<kFromQ>(p, d, qc, lane)) return false;
+    long long tPh = ff.wst ? clock64() : 0;
+    if (ff.count > 0) preW = peek_prefix(p, ff.blk[ff.head]);
+    if (!kFromQ && !(d.flags & kDescQuant) && !wait_quant(p, d)) return false;
+    const uint32_t top = (1u << d.depth) - 1u;
+    const bool biased = d.depth <= 23;
+    MNW_PHASE(0)
 
     const int len = d.len;
     uint32_t q[kChunk];
@@ -153,7 +143,7 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, const WorkDesc &d
             q[i] = e < len ? (uint32_t)qsrc[e] : 0u;
         }
     } else {
-        if (d.slow) {
+        if (d.flags & kDescSlow) {
             // ragged or unaligned block: plain loads into the stage, same swizzled layout
             const DevField *fdp = p.fields + d.f;
             const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
@@ -166,33 +156,42 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, const WorkDesc &d
             }
             __syncwarp();
         }
-        if (qc.isPos) {
-            if (qc.biased) quantise32<true, true>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
-            else quantise32<true, false>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
+        Unwrap uw;
+        uw.tHi = d.tHi;
+        uw.tLo = d.tLo;
+        uw.L = d.L;
+        if (d.flags & kDescPos) {
+            if (biased) quantise32<true, true>(stage, lane, uw, d.x0, d.scale, top, q);
+            else quantise32<true, false>(stage, lane, uw, d.x0, d.scale, top, q);
         } else {
-            if (qc.biased) quantise32<false, true>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
-            else quantise32<false, false>(stage, lane, qc.uw, qc.x0, qc.scale, qc.top, q);
+            if (biased) quantise32<false, true>(stage, lane, uw, d.x0, d.scale, top, q);
+            else quantise32<false, false>(stage, lane, uw, d.x0, d.scale, top, q);
         }
     }
 
+    MNW_PHASE(1)
     BlockStats bs = delta_width(q, len, lane, p.error);
-    if (!kFromQ && qc.biased) bs.first -= kQBias;
+    if (!kFromQ && biased) bs.first -= kQBias;
     const int nWords = (len * bs.w + 31) >> 5;
     const uint32_t size16 = (uint32_t)((nWords + 3) >> 2);
     // the size is all the scan warp needs: publish it before anything else
     if (lane == 0)
-        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.blkAgg + blk), "r"(kAggReady | size16) : "memory");
+        asm volatile("st.relaxed.gpu.global.u16 [%0], %1;" ::"l"(p.blkAgg + blk), "h"((uint16_t)(kAggReady | size16)) : "memory");
 
     // pack through the block's own stage (its values are in registers by now)
     uint32_t *tmp = reinterpret_cast<uint32_t *>(stage);
     __syncwarp();
+    MNW_PHASE(2)
     if (bs.w > 0) pack_dispatch(bs.w, q, tmp, lane);
     __syncwarp();
-    if (ff.count == kFifo) {  // no free slot: the oldest block has to go now
+    MNW_PHASE(3)
+    if (ff.count == kFifo) {
+        if (ff.wst && lane == 0) ff.wst[7] += 1;  // no free slot: the oldest block has to go now
         if (!place_oldest(p, ff, preW, lane)) return false;
         preW = 0;
-        if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
+        if (ff.count > 0) preW = peek_prefix(p, ff.blk[ff.head]);
     }
+    MNW_PHASE(4)
     const int k = (ff.head + ff.count) % kFifo;
     uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
     for (int c = lane; c < (int)size16; c += 32) {
@@ -210,12 +209,17 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, const WorkDesc &d
     }
     ff.count++;
     release_stage(rc, s, true, lane);  // includes __syncwarp
-    // place whatever has its prefix already (normally exactly one block per block packed)
-    while (ff.count > 0 && (preW & kPrefixReady)) {
+    MNW_PHASE(5)
+    // normally one block out per block in; more only when the parked blocks pile up
+    if (ff.count > 0 && (preW & kPrefixReady)) {
         if (!place_oldest(p, ff, preW, lane)) return false;
-        preW = 0;
-        if (ff.count > 0) preW = ld_relaxed_u64(p.blkPrefix + ff.blk[ff.head]);
+        while (ff.count > kFifo / 2) {
+            preW = peek_prefix(p, ff.blk[ff.head]);
+            if (!(preW & kPrefixReady)) break;
+            if (!place_oldest(p, ff, preW, lane)) return false;
+        }
     }
+    MNW_PHASE(6)
     return true;
 }
 

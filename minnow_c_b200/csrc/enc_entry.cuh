@@ -35,18 +35,21 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         else if (blockIdx.x == 1 && p.lagG >= 0 && !kFromQ) reduce_fields(p, lane);
         return;
     }
-    UnwrapCache uc;
-    uc.f = uc.comp = -1;
-    uc.isPos = false;
-    uc.uw.tHi = uc.uw.tLo = uc.uw.L = 0.0f;
-    QuantCache qc;
-    qc.f = qc.comp = -1;
     const int c = warp - 1;
     ParkFifo ff;
     ff.rec = reinterpret_cast<uint4 *>(encSmem + kEncFifoOff) + c * kFifo;
     ff.blk = reinterpret_cast<int64_t *>(encSmem + kEncFifoOff + kEncConsumers * kFifo * 16) + c * kFifo;
     ff.slots = p.scratch + ((size_t)blockIdx.x * kEncConsumers + c) * kFifo * kSlotWords;
     ff.head = ff.count = 0;
+    ff.p0Field = -1;
+    ff.p0 = 0;
+    ff.wst = nullptr;
+    if (p.stats) {
+        ff.wst = reinterpret_cast<unsigned long long *>(encSmem + kEncStatOff) + c * 8;
+        if (lane == 0)
+            for (int i = 0; i < 8; i++) ff.wst[i] = 0;
+        __syncwarp();
+    }
     bool drain = false;
     long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0;
     const long long tStart = clock64();
@@ -61,7 +64,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             if (++spins > (kSpinLimit << 6)) { spin_timeout(p.error, 7, -1); return; }
         }
         if (!mbar_wait(p.error, rc.full + s, use & 1u, 5)) return;
-        const WorkDesc d = rc.desc[s];
+        WorkDesc d = rc.desc[s];
         float *stage = reinterpret_cast<float *>(encSmem + kEncRingOff + s * kEncStageBytes);
         const long long c1 = clock64();
         tQueue += c1 - c0;
@@ -71,12 +74,12 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             continue;
         }
         if (d.kind == kWorkA) {
-            a_block(p, d, stage, uc, lane);
+            a_block(p, d, stage, lane);
             release_stage(rc, s, false, lane);
             tA += clock64() - c1;
             nA++;
         } else if (d.kind == kWorkB) {
-            if (!b_block<kFromQ>(p, d, stage, rc, s, qc, ff, lane)) {
+            if (!b_block<kFromQ>(p, d, stage, rc, s, ff, lane)) {
                 drain = true;
                 release_stage(rc, s, false, lane);
                 continue;
@@ -96,6 +99,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         atomicAdd(p.stats + 5, (unsigned long long)nA);
         atomicAdd(p.stats + 6, (unsigned long long)nB);
         atomicAdd(p.stats + 7, (unsigned long long)(clock64() - tStart));
+        for (int i = 0; i < 8; i++) atomicAdd(p.stats + 8 + i, ff.wst[i]);
     }
 }
 
@@ -107,11 +111,14 @@ __global__ void __launch_bounds__(128) k_finalize(EncodeParams p, int64_t fixedT
     const int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f > p.nFields) return;
     if (f == p.nFields) {
-        p.offsets[f] = (uint64_t)fixedTotal + (p.blkPrefix[p.nBlocks] & ~kPrefixReady) * 16;
+        p.offsets[f] = (uint64_t)fixedTotal + (p.winBase[(p.nBlocks + kScanWin - 1) / kScanWin] & ~kPrefixReady) * 16;
         return;
     }
     const DevField fd = p.fields[f];
-    const uint64_t p0 = p.blkPrefix[fd.firstBlock] & ~kPrefixReady;
+    // an empty field at the very end has no first block: its region starts at the total
+    const uint64_t p0 = fd.firstBlock < p.nBlocks
+                            ? (p.winBase[fd.firstBlock / kScanWin] & ~kPrefixReady) + (p.blkRel[fd.firstBlock] & ~kRelReady)
+                            : (p.winBase[(p.nBlocks + kScanWin - 1) / kScanWin] & ~kPrefixReady);
     const int64_t regionStart = fd.fixedBase + (int64_t)(p0 * 16);
     p.offsets[f] = (uint64_t)regionStart;
     if (regionStart + 64 + (int64_t)fd.nb * 48 > p.outCap) { atomicCAS(p.error, 0, kErrCapacity); return; }

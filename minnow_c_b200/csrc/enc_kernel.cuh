@@ -81,24 +81,46 @@ __global__ void k_depth_empty(EncodeParams p) {
 }
 
 // ---------------------------------------------------------------------------
-// Scan warp: block sizes -> exclusive prefixes, 1024 blocks per poll. The flag
-// words carry their own payload and nobody reads anything else through them,
-// so relaxed accesses are enough.
+// Scan warp: block sizes -> exclusive prefixes, one window of 1024 blocks at a
+// time with the next window's loads already in flight. Sizes are 16-bit words
+// (8 blocks per 16-byte load); a block's prefix goes out as a 32-bit offset
+// within its window plus one 64-bit base per window. The words carry their own
+// "there" bits and nobody reads anything else through them: relaxed accesses.
+// Lane l, load j covers blocks base + 256 j + 8 l .. +7 (coalesced).
 // ---------------------------------------------------------------------------
-constexpr int kScanPerLane = 32;
+__device__ __forceinline__ bool agg_ready(const uint4 &v) {
+    return (v.x & v.y & v.z & v.w & 0x80008000u) == 0x80008000u;
+}
+__device__ __forceinline__ void scan_load(const EncodeParams &p, int64_t base, int lane, uint4 (&a)[4]) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) a[j] = ld_relaxed_u4(p.blkAgg + base + j * 256 + lane * 8);
+}
 
 __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
     uint64_t running = 0;
-    for (int64_t base = 0; base < p.nBlocks; base += 32 * kScanPerLane) {
-        const int64_t mine = base + (int64_t)lane * kScanPerLane;
-        uint32_t a[kScanPerLane];
+    uint4 cur[4], nxt[4];
+    scan_load(p, 0, lane, cur);
+    int64_t w = 0;
+    for (int64_t base = 0; base < p.nBlocks; base += kScanWin, w++) {
+        if (lane == 0)
+            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p.winBase + w), "l"(kPrefixReady | running) : "memory");
+        const bool more = base + kScanWin < p.nBlocks;
+        if (more) scan_load(p, base + kScanWin, lane, nxt);
+        if (base + kScanWin > p.nBlocks) {
+            // last, ragged window: blocks past the end count as there, with size 0
 #pragma unroll
-        for (int k = 0; k < kScanPerLane; k++) a[k] = mine + k < p.nBlocks ? ld_relaxed_u32(p.blkAgg + mine + k) : kAggReady;
+            for (int j = 0; j < 4; j++) {
+                uint32_t *wds = reinterpret_cast<uint32_t *>(&cur[j]);
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    if (base + j * 256 + lane * 8 + i >= p.nBlocks) wds[i >> 1] = (wds[i >> 1] & ~(0xffffu << (16 * (i & 1)))) | (kAggReady << (16 * (i & 1)));
+            }
+        }
         uint32_t spins = 0;
         while (true) {
             bool all = true;
 #pragma unroll
-            for (int k = 0; k < kScanPerLane; k++) all = all && (a[k] & kAggReady);
+            for (int j = 0; j < 4; j++) all = all && agg_ready(cur[j]);
             if (__all_sync(kFull, all)) break;
             if (++spins > kSpinLimit) {
                 if (lane == 0) spin_timeout(p.error, 3, base);
@@ -106,39 +128,62 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
             }
             if (spins > 16) __nanosleep(100);
 #pragma unroll
-            for (int k = 0; k < kScanPerLane; k++)
-                if (!(a[k] & kAggReady)) a[k] = ld_relaxed_u32(p.blkAgg + mine + k);
+            for (int j = 0; j < 4; j++)
+                if (!agg_ready(cur[j])) {
+                    uint4 v = ld_relaxed_u4(p.blkAgg + base + j * 256 + lane * 8);
+                    if (base + kScanWin > p.nBlocks) {
+                        uint32_t *wds = reinterpret_cast<uint32_t *>(&v);
+#pragma unroll
+                        for (int i = 0; i < 8; i++)
+                            if (base + j * 256 + lane * 8 + i >= p.nBlocks) wds[i >> 1] = (wds[i >> 1] & ~(0xffffu << (16 * (i & 1)))) | (kAggReady << (16 * (i & 1)));
+                    }
+                    cur[j] = v;
+                }
         }
-        uint32_t local = 0;
+        uint32_t rowBase = 0;
 #pragma unroll
-        for (int k = 0; k < kScanPerLane; k++) local += a[k] & ~kAggReady;
-        uint32_t incl = local;
+        for (int j = 0; j < 4; j++) {
+            const uint32_t wd[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
+            uint32_t sz[8];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t up = __shfl_up_sync(kFull, incl, d);
-            if (lane >= d) incl += up;
-        }
-        uint64_t excl = running + (incl - local);
+            for (int i = 0; i < 8; i++) sz[i] = (wd[i >> 1] >> (16 * (i & 1))) & 0x7fffu;
+            uint32_t mine = 0;
 #pragma unroll
-        for (int k = 0; k < kScanPerLane; k++) {
-            if (mine + k < p.nBlocks) {
-                asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p.blkPrefix + mine + k),
-                             "l"(kPrefixReady | excl) : "memory");
+            for (int i = 0; i < 8; i++) mine += sz[i];
+            uint32_t incl = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t up = __shfl_up_sync(kFull, incl, d);
+                if (lane >= d) incl += up;
             }
-            excl += a[k] & ~kAggReady;
+            uint32_t ex = kRelReady | (rowBase + incl - mine);
+            uint32_t o[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                o[i] = ex;
+                ex += sz[i];
+            }
+            uint32_t *dst = p.blkRel + base + j * 256 + lane * 8;
+            st_relaxed_u4(dst, make_uint4(o[0], o[1], o[2], o[3]));
+            st_relaxed_u4(dst + 4, make_uint4(o[4], o[5], o[6], o[7]));
+            rowBase += __shfl_sync(kFull, incl, 31);
         }
-        running += __shfl_sync(kFull, incl, 31);
+        running += rowBase;
+        if (more) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) cur[j] = nxt[j];
+        }
     }
-    if (lane == 0) st_release_u64(p.blkPrefix + p.nBlocks, kPrefixReady | running);
+    if (lane == 0)
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p.winBase + w), "l"(kPrefixReady | running) : "memory");
 }
 
 // ---------------------------------------------------------------------------
 // Reduce warp: block min/max -> per-component min/max -> the field's
-// parameters, in block order, 512 blocks per poll. All lanes walk the
-// (field, component) sequence together.
+// parameters, in block order, one window of 512 blocks at a time with the next
+// window's loads in flight. All lanes walk the (field, component) sequence
+// together. Lane l, load j covers blocks base + 64 j + 2 l, +1.
 // ---------------------------------------------------------------------------
-constexpr int kRedPerLane = 16;
-
 struct RedWalk {
     int f, comp;
     int64_t compEnd;  // global index one past the component's last block
@@ -167,25 +212,39 @@ __device__ __forceinline__ void red_finish_comp(const EncodeParams &p, RedWalk &
     }
 }
 
+__device__ __forceinline__ bool mm_ready(const uint4 &v) { return (v.x | v.y) != 0u && (v.z | v.w) != 0u; }
+__device__ __forceinline__ void red_load(const EncodeParams &p, int64_t base, int lane, uint4 (&a)[8]) {
+#pragma unroll
+    for (int j = 0; j < 8; j++) a[j] = ld_relaxed_u4(p.blkMM + base + j * 64 + lane * 2);
+}
+
 __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
     RedWalk w;
     w.f = w.comp = 0;
     w.compEnd = 0;
     w.lo = w.hi = 0xffffffffu;
     red_skip_empty(p, w);
-    constexpr int kWin = 32 * kRedPerLane;
-    for (int64_t base = 0; base < p.nBlocks; base += kWin) {
-        uint64_t a[kRedPerLane];
-#pragma unroll
-        for (int k = 0; k < kRedPerLane; k++) {
-            const int64_t blk = base + k * 32 + lane;
-            a[k] = blk < p.nBlocks ? ld_relaxed_u64(p.blkMM + blk) : ~0ull;
-        }
+    uint4 cur[8], nxt[8];
+    red_load(p, 0, lane, cur);
+    for (int64_t base = 0; base < p.nBlocks; base += kRedWin) {
+        const bool more = base + kRedWin < p.nBlocks;
+        if (more) red_load(p, base + kRedWin, lane, nxt);
+        const int64_t winEnd = min(base + kRedWin, p.nBlocks);
+        const bool whole = base + kRedWin <= p.nBlocks;
         uint32_t spins = 0;
         while (true) {
             bool all = true;
+            if (whole) {
 #pragma unroll
-            for (int k = 0; k < kRedPerLane; k++) all = all && a[k] != 0ull;
+                for (int j = 0; j < 8; j++) all = all && mm_ready(cur[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int64_t b0 = base + j * 64 + lane * 2;
+                    all = all && (b0 >= winEnd || (cur[j].x | cur[j].y) != 0u) &&
+                          (b0 + 1 >= winEnd || (cur[j].z | cur[j].w) != 0u);
+                }
+            }
             if (__all_sync(kFull, all)) break;
             if (++spins > kSpinLimit) {
                 if (lane == 0) spin_timeout(p.error, 6, base);
@@ -193,35 +252,47 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
             }
             if (spins > 16) __nanosleep(100);
 #pragma unroll
-            for (int k = 0; k < kRedPerLane; k++)
-                if (a[k] == 0ull) a[k] = ld_relaxed_u64(p.blkMM + base + k * 32 + lane);
+            for (int j = 0; j < 8; j++)
+                if (!mm_ready(cur[j])) cur[j] = ld_relaxed_u4(p.blkMM + base + j * 64 + lane * 2);
         }
-        if (base + kWin <= w.compEnd && !(p.dbg & 1)) {
-            // the whole window lies in one component
+        if (whole && base + kRedWin <= w.compEnd) {
+            // the usual case: the whole window lies in one component
             uint32_t lo = 0xffffffffu, hi = 0xffffffffu;
 #pragma unroll
-            for (int k = 0; k < kRedPerLane; k++) {
-                lo = min(lo, (uint32_t)a[k]);
-                hi = min(hi, (uint32_t)(a[k] >> 32));
+            for (int j = 0; j < 8; j++) {
+                lo = min(lo, min(cur[j].x, cur[j].z));
+                hi = min(hi, min(cur[j].y, cur[j].w));
             }
             w.lo = min(w.lo, __reduce_min_sync(kFull, lo));
             w.hi = min(w.hi, __reduce_min_sync(kFull, hi));
-            if (base + kWin == w.compEnd) red_finish_comp(p, w, lane);
+            if (base + kRedWin == w.compEnd) red_finish_comp(p, w, lane);
         } else {
+            // component by component
+            int64_t s0 = base;
+            while (s0 < winEnd) {
+                const int64_t e = min(winEnd, w.compEnd);
+                uint32_t lo = 0xffffffffu, hi = 0xffffffffu;
 #pragma unroll
-            for (int k = 0; k < kRedPerLane; k++) {
-                int64_t s0 = base + k * 32;
-                const int64_t s1 = min(s0 + 32, p.nBlocks);
-                const int64_t blk = s0 + lane;
-                while (s0 < s1) {
-                    const int64_t e = min(s1, w.compEnd);
-                    const bool in = blk >= s0 && blk < e;
-                    w.lo = min(w.lo, __reduce_min_sync(kFull, in ? (uint32_t)a[k] : 0xffffffffu));
-                    w.hi = min(w.hi, __reduce_min_sync(kFull, in ? (uint32_t)(a[k] >> 32) : 0xffffffffu));
-                    s0 = e;
-                    if (s0 == w.compEnd) red_finish_comp(p, w, lane);
+                for (int j = 0; j < 8; j++) {
+                    const int64_t b0 = base + j * 64 + lane * 2;
+                    if (b0 >= s0 && b0 < e) {
+                        lo = min(lo, cur[j].x);
+                        hi = min(hi, cur[j].y);
+                    }
+                    if (b0 + 1 >= s0 && b0 + 1 < e) {
+                        lo = min(lo, cur[j].z);
+                        hi = min(hi, cur[j].w);
+                    }
                 }
+                w.lo = min(w.lo, __reduce_min_sync(kFull, lo));
+                w.hi = min(w.hi, __reduce_min_sync(kFull, hi));
+                s0 = e;
+                if (s0 == w.compEnd) red_finish_comp(p, w, lane);
             }
+        }
+        if (more) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) cur[j] = nxt[j];
         }
     }
 }
@@ -229,12 +300,6 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
 // ---------------------------------------------------------------------------
 // A work: min/max of one block
 // ---------------------------------------------------------------------------
-struct UnwrapCache {  // of the component a consumer last did A work on
-    int f, comp;      // -1: empty
-    Unwrap uw;
-    bool isPos;
-};
-
 template <bool kPos>
 __device__ __forceinline__ void minmax_stage(const float4 *st, int lane, const Unwrap &uw, float &lo, float &hi) {
 #pragma unroll
@@ -252,34 +317,30 @@ __device__ __forceinline__ void minmax_stage(const float4 *st, int lane, const U
     }
 }
 
-__device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d, const float *stage, UnwrapCache &uc,
-                                        int lane) {
-    if (uc.f != d.f || uc.comp != d.comp) {
-        const DevField *fdp = p.fields + d.f;
-        uc.f = d.f;
-        uc.comp = d.comp;
-        uc.isPos = fdp->fieldCode == field_Posn;
-        uc.uw.tHi = uc.uw.tLo = uc.uw.L = 0.0f;
-        if (uc.isPos) uc.uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * fdp->n), fdp->width);
-    }
+__device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d, const float *stage, int lane) {
+    const bool isPos = d.flags & kDescPos;
+    Unwrap uw;
+    uw.tHi = d.tHi;
+    uw.tLo = d.tLo;
+    uw.L = d.L;
     float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
-    if (!d.slow) {
+    if (!(d.flags & kDescSlow)) {
         const float4 *st = reinterpret_cast<const float4 *>(stage);
-        if (uc.isPos) minmax_stage<true>(st, lane, uc.uw, lo, hi);
-        else minmax_stage<false>(st, lane, uc.uw, lo, hi);
+        if (isPos) minmax_stage<true>(st, lane, uw, lo, hi);
+        else minmax_stage<false>(st, lane, uw, lo, hi);
     } else {
         const DevField *fdp = p.fields + d.f;
         const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
         for (int i = lane; i < d.len; i += 32) {
             float u = __ldg(src + i);
-            if (uc.isPos) u = unwrap_t(u, uc.uw);
+            if (isPos) u = unwrap_t(u, uw);
             lo = fminf(lo, u);
             hi = fmaxf(hi, u);
         }
     }
     const uint32_t olo = __reduce_min_sync(kFull, ord_from_float(lo));
     const uint32_t ohi = __reduce_min_sync(kFull, ~ord_from_float(hi));  // max kept inverted: one min for both
-    if (lane == 0)
+    if (lane == 0)  // never all-zero: min is never NaN
         asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p.blkMM + d.blk),
                      "l"((uint64_t)olo | ((uint64_t)ohi << 32)) : "memory");
 }

@@ -12,16 +12,27 @@
 // been handed back (a plain counter), and only then for the fill.
 #pragma once
 
-#include "enc_common.cuh"
+#include "enc_math.cuh"
 
 namespace mnw {
 
-struct WorkDesc {  // 32 bytes, one per ring stage
+struct WorkDesc {  // 64 bytes, one per ring stage: the block and what its component needs
     int32_t kind;
     int32_t f, comp, b;
     int64_t blk;
     int32_t len;
-    uint32_t slow;  // the block did not go through the TMA: the consumer loads it itself
+    uint32_t flags;   // kDescSlow | kDescPos | kDescQuant
+    double scale;     // util_UniformBinIndex's 2^depth / maxDiff (kDescQuant)
+    float x0;
+    uint32_t depth;
+    float tHi, tLo;   // unwrap thresholds (kDescPos), see make_unwrap
+    float L;
+    uint32_t pad;
+};
+enum : uint32_t {
+    kDescSlow = 1u,   // the block did not go through the TMA: the consumer loads it itself
+    kDescPos = 2u,    // a position component: periodic unwrap applies
+    kDescQuant = 4u,  // scale, x0 and depth are filled in (else the consumer waits for them)
 };
 
 struct RingCtrl {
@@ -98,6 +109,16 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                                          const RingCtrl &rc, int lane) {
     const uint64_t keep = l2_policy_keep(), drop = l2_policy_drop();
     const bool onlyB = kFromQ || p.lagG < 0;
+    struct {
+        int f, comp;
+        uint32_t flags, depth;
+        float L, tHi, tLo, x0;
+        double scale;
+    } pc;
+    pc.f = pc.comp = -1;
+    pc.flags = pc.depth = 0;
+    pc.L = pc.tHi = pc.tLo = pc.x0 = 0.0f;
+    pc.scale = 0.0;
     uint32_t pass = 0;
     uint32_t tk = 0;
     if (lane == 0) tk = atomicAdd(p.ticket, 1u);
@@ -109,7 +130,11 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         d.kind = kWorkNop;
         d.f = d.comp = d.b = 0;
         d.len = 0;
-        d.slow = 1;
+        d.flags = kDescSlow;
+        d.scale = 0.0;
+        d.x0 = d.tHi = d.tLo = d.L = 0.0f;
+        d.depth = 0;
+        d.pad = 0;
         int64_t blk;
         if (onlyB) {
             blk = g * kGroupSlots + lane;
@@ -133,7 +158,48 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
             row = (p.tmaShift + off) >> 5;
             fast = !kFromQ && p.tmaShift >= 0 && d.len == kBlockLen && ((p.tmaShift + off) & 31) == 0 &&
                    row + 32 <= p.tmaRows;
-            d.slow = fast ? 0u : 1u;
+            // the component's constants: this lane sees the same component for many passes
+            if (pc.f != d.f || pc.comp != d.comp) {
+                pc.f = d.f;
+                pc.comp = d.comp;
+                pc.flags = 0;
+                pc.L = fdp->width;
+                pc.tHi = pc.tLo = pc.x0 = 0.0f;
+                pc.scale = 0.0;
+                pc.depth = 0;
+                if (!kFromQ && fdp->fieldCode == field_Posn) {
+                    const Unwrap uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * n), fdp->width);
+                    pc.tHi = uw.tHi;
+                    pc.tLo = uw.tLo;
+                    pc.flags |= kDescPos;
+                }
+            }
+            if (d.kind == kWorkB && !kFromQ && !(pc.flags & kDescQuant)) {
+                if (p.lagG >= 0) {
+                    // published during this launch by the reduce warp; if not there yet the consumer waits
+                    const uint64_t *w = p.fq + ((int64_t)d.f * 3 + d.comp) * 2;
+                    const uint64_t w0 = ld_relaxed_u64(w), w1 = ld_relaxed_u64(w + 1);
+                    if (w0 & w1 & kFqValid) {
+                        pc.scale = __longlong_as_double((long long)(w0 & ~kFqValid));
+                        pc.x0 = __uint_as_float((uint32_t)w1);
+                        pc.depth = (uint32_t)(w1 >> 32) & 0xffu;
+                        pc.flags |= kDescQuant;
+                    }
+                } else {
+                    const DevQuant *qp = p.quant + d.f;  // given by the caller, written before the launch
+                    pc.x0 = __ldg(&qp->X0[d.comp]);
+                    pc.scale = __ldg(&qp->scale);
+                    pc.depth = __ldg(&qp->depth);
+                    pc.flags |= kDescQuant;
+                }
+            }
+            d.flags = pc.flags | (fast ? 0u : kDescSlow);
+            d.scale = pc.scale;
+            d.x0 = pc.x0;
+            d.depth = pc.depth;
+            d.tHi = pc.tHi;
+            d.tLo = pc.tLo;
+            d.L = pc.L;
         }
         const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
         const int s = (int)(seq % kEncStages);
@@ -159,7 +225,10 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         d.f = d.comp = d.b = 0;
         d.blk = -1;
         d.len = 0;
-        d.slow = 1;
+        d.flags = kDescSlow;
+        d.scale = 0.0;
+        d.x0 = d.tHi = d.tLo = d.L = 0.0f;
+        d.depth = d.pad = 0;
         rc.desc[s] = d;
         mbar_arrive(rc.full + s);
     }

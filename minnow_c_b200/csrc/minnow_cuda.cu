@@ -183,8 +183,8 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
             MNW_PANIC("cuTensorMapEncodeTiled is not available from this driver.");
     }
     if (getenv("MNWCUDA_ENCODE_STATS")) {
-        CUDA_CHECK(cudaMalloc(&ctx->encStats, 64));
-        CUDA_CHECK(cudaMemset(ctx->encStats, 0, 64));
+        CUDA_CHECK(cudaMalloc(&ctx->encStats, 128));
+        CUDA_CHECK(cudaMemset(ctx->encStats, 0, 128));
     }
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
@@ -209,13 +209,17 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     for (cudaEvent_t e : ctx->ev)
         if (e) cudaEventDestroy(e);
     if (ctx->encStats) {
-        unsigned long long h[8];
+        unsigned long long h[16];
         cudaMemcpy(h, ctx->encStats, sizeof(h), cudaMemcpyDeviceToHost);
         const double tot = (double)h[7] > 0 ? (double)h[7] : 1.0;
         fprintf(stderr, "[mnwcuda encode stats] consumer-time shares: A %.1f%% B %.1f%% queue %.1f%% | clk/A-block %.0f "
                         "clk/B-block %.0f | blocks A %llu B %llu\n",
                 100.0 * h[0] / tot, 100.0 * h[1] / tot, 100.0 * h[4] / tot, (double)h[0] / (double)(h[5] ? h[5] : 1),
                 (double)h[1] / (double)(h[6] ? h[6] : 1), h[5], h[6]);
+        const double nB = (double)(h[6] ? h[6] : 1);
+        fprintf(stderr, "[mnwcuda encode stats] clk/B-block by phase: params %.0f quantise %.0f delta+width %.0f pack %.0f "
+                        "forced-place %.0f park %.0f place %.0f | forced placements %.1f%%\n",
+                h[8] / nB, h[9] / nB, h[10] / nB, h[11] / nB, h[12] / nB, h[13] / nB, h[14] / nB, 100.0 * h[15] / nB);
         cudaFree(ctx->encStats);
     }
     delete ctx;
@@ -267,16 +271,17 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
                         (long long)q.nGroups, (long long)q.lagG, st[0]);
                 // first block without a prefix / a size / a min-max, first component without parameters
                 const size_t nb = (size_t)q.nBlocks;
-                std::vector<uint64_t> pre(nb + 1), mm(nb), fq((size_t)q.nFields * 6);
-                std::vector<uint32_t> agg(nb);
-                cudaMemcpy(pre.data(), q.blkPrefix, (nb + 1) * 8, cudaMemcpyDeviceToHost);
+                std::vector<uint64_t> mm(nb), fq((size_t)q.nFields * 6);
+                std::vector<uint32_t> pre(nb);
+                std::vector<uint16_t> agg(nb);
+                cudaMemcpy(pre.data(), q.blkRel, nb * 4, cudaMemcpyDeviceToHost);
                 cudaMemcpy(mm.data(), q.blkMM, nb * 8, cudaMemcpyDeviceToHost);
-                cudaMemcpy(agg.data(), q.blkAgg, nb * 4, cudaMemcpyDeviceToHost);
+                cudaMemcpy(agg.data(), q.blkAgg, nb * 2, cudaMemcpyDeviceToHost);
                 cudaMemcpy(fq.data(), q.fq, fq.size() * 8, cudaMemcpyDeviceToHost);
                 size_t iPre = 0, iAgg = 0, iMM = 0, iFq = 0, nAggMissing = 0;
-                while (iPre <= nb && (pre[iPre] >> 63)) iPre++;
-                while (iAgg < nb && (agg[iAgg] >> 31)) iAgg++;
-                for (size_t i = 0; i < nb; i++) nAggMissing += !(agg[i] >> 31);
+                while (iPre < nb && (pre[iPre] >> 31)) iPre++;
+                while (iAgg < nb && (agg[iAgg] >> 15)) iAgg++;
+                for (size_t i = 0; i < nb; i++) nAggMissing += !(agg[i] >> 15);
                 while (iMM < nb && mm[iMM]) iMM++;
                 while (iFq < fq.size() && (fq[iFq] >> 63)) iFq++;
                 fprintf(stderr, "[mnwcuda] first missing: prefix %zu size %zu (missing in all %zu) minmax %zu params word %zu of %zu\n",
@@ -357,13 +362,20 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     // per-consumer scratch slots for packed blocks waiting for their offset
     p.scratch = static_cast<uint32_t *>(
         ctx->ring.need((size_t)ctx->smCount * kEncConsumers * kFifo * kSlotWords * sizeof(uint32_t)));
-    // one zeroed region: block prefixes | block min/max | component parameters | block sizes | ticket
-    const size_t stateWords = (size_t)(pl.nBlocks + 1) * 2 + (size_t)pl.nBlocks * 2 + 12 * nF + (size_t)pl.nBlocks + 2;
-    p.blkPrefix = static_cast<uint64_t *>(ctx->tileState.need(stateWords * sizeof(uint32_t)));
-    p.blkMM = p.blkPrefix + pl.nBlocks + 1;
-    p.fq = p.blkMM + pl.nBlocks;
-    p.blkAgg = reinterpret_cast<uint32_t *>(p.fq + 6 * nF);
-    p.ticket = p.blkAgg + pl.nBlocks;
+    // one zeroed region: window bases | block min/max | component parameters | block prefixes | block sizes | ticket
+    const size_t nWin = (size_t)((pl.nBlocks + kScanWin - 1) / kScanWin);
+    const size_t padScan = nWin * kScanWin;
+    const size_t padRed = (size_t)((pl.nBlocks + kRedWin - 1) / kRedWin) * kRedWin;
+    const size_t bWin = ((nWin + 1) * 8 + 15) & ~(size_t)15, bMM = padRed * 8, bFq = nF * 6 * 8;
+    const size_t bRel = padScan * 4, bAgg = padScan * 2;
+    const size_t stateBytes = bWin + bMM + bFq + bRel + bAgg + 16;
+    uint8_t *st = static_cast<uint8_t *>(ctx->tileState.need(stateBytes));
+    p.winBase = reinterpret_cast<uint64_t *>(st);
+    p.blkMM = reinterpret_cast<uint64_t *>(st + bWin);
+    p.fq = reinterpret_cast<uint64_t *>(st + bWin + bMM);
+    p.blkRel = reinterpret_cast<uint32_t *>(st + bWin + bMM + bFq);
+    p.blkAgg = reinterpret_cast<uint16_t *>(st + bWin + bMM + bFq + bRel);
+    p.ticket = reinterpret_cast<uint32_t *>(st + bWin + bMM + bFq + bRel + bAgg);
     p.out = d_out;
     p.outCap = outCap;
     p.offsets = d_offsets;
@@ -373,7 +385,7 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     // pageable source: the copy is staged before the call returns
     CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), nF * sizeof(DevField),
                                cudaMemcpyHostToDevice, s));
-    CUDA_CHECK(cudaMemsetAsync(p.blkPrefix, 0, stateWords * sizeof(uint32_t), s));
+    CUDA_CHECK(cudaMemsetAsync(st, 0, stateBytes, s));
     return p;
 }
 
