@@ -107,6 +107,8 @@ __device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
 template <bool kFromQ>
 __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMap *map, uint8_t *smem,
                                          const RingCtrl &rc, int lane) {
+    // the A-to-B distance is more than L2 holds next to the parked blocks and the
+    // flag arrays: both reads are streamed (MNWCUDA_DBG=2 keeps the A read instead)
     const uint64_t keep = l2_policy_keep(), drop = l2_policy_drop();
     const bool onlyB = kFromQ || p.lagG < 0;
     struct {
@@ -209,7 +211,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         if (fast) {
             mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
             tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
-                           d.kind == kWorkA ? keep : drop);
+                           (d.kind == kWorkA && (p.dbg & 2)) ? keep : drop);
         } else {
             mbar_arrive(rc.full + s);
         }
