@@ -99,7 +99,10 @@ int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in,
 /* Waits for `stream` and returns 0 or the first device-side error of the
  * calls since the last Status: 1 = accuracy needs depth > 24 (the Panic of
  * src/quant.c:688-693), 2 = output capacity exceeded, 3 = malformed payload,
- * 4 = quantised integers at the CFunc boundary exceed 24 bits. */
+ * 4 = quantised integers at the CFunc boundary exceed 24 bits,
+ * 5 = a device-side wait inside k_encode timed out (an internal error: the
+ *     kernel ends cleanly, the output is invalid, and a description of the
+ *     first missing dependency goes to stderr). */
 int mnwcuda_Status(MnwCudaCtx *ctx, void *stream);
 /* Kernels launched by this context since creation (bench bookkeeping). */
 int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx);
