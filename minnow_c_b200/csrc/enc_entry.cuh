@@ -26,6 +26,10 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         fence_proxy_async();
     }
     __syncthreads();
+    // with enough CTAs the first two do nothing but scan and reduce: a service warp that
+    // shares its SM with 14 busy consumers falls behind, and everybody waits for it
+    const bool service = gridDim.x >= 8 && blockIdx.x < 2;
+    if (service && warp != kEncWarps - 1) return;
     if (warp == 0) {
         producer<kFromQ>(p, &tmap, encSmem, rc, lane);
         return;
