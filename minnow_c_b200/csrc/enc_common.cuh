@@ -23,8 +23,8 @@
 namespace mnw {
 
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kEncWarps = 16;        // per CTA (one CTA per SM): producer, 14 consumers, scan warp (CTA 0 only)
-constexpr int kEncConsumers = 14;
+constexpr int kEncWarps = 20;        // per CTA (one CTA per SM): producer, 18 consumers, a service warp (scan in CTA 0, reduce in CTA 1)
+constexpr int kEncConsumers = 18;
 constexpr int kEncStages = 48;       // input ring: 4 KiB blocks per SM (TMA, 128-byte swizzle)
 constexpr int kEncStageBytes = 4096;
 constexpr int kGroupSlots = 32;      // slots per ticket

@@ -64,18 +64,13 @@ __device__ __forceinline__ uint64_t peek_prefix(const EncodeParams &p, int64_t b
     return block_prefix(p.blkRel, p.winBase, blk, pre) ? (kPrefixReady | pre) : 0ull;
 }
 
-// copy the oldest parked block to its final position and write its table entry
-__device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff, uint64_t preW, int lane) {
+// The oldest parked block goes to its final position: `pre` is its prefix, rv its
+// record, v0/v1 its first two 16-byte chunks per lane (already loaded by the
+// caller so that their latency overlaps other work); wider blocks load the rest here.
+__device__ __forceinline__ void place_finish(const EncodeParams &p, ParkFifo &ff, uint64_t pre, const uint4 &rv,
+                                             const uint4 &v0, const uint4 &v1, int lane) {
     const int k = ff.head;
     const int64_t pl = ff.blk[k];
-    uint64_t pre = preW & ~kPrefixReady;
-    if (!(preW & kPrefixReady)) {
-        uint32_t spins = 0;
-        while (!block_prefix(p.blkRel, p.winBase, pl, pre)) {
-            __nanosleep(200);
-            if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); return false; }
-        }
-    }
     int f, comp, b;
     locate_block(p, pl, f, comp, b);
     const DevField *fdp = p.fields + f;
@@ -87,7 +82,6 @@ __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff
         ff.p0Field = f;
     }
     const uint64_t p0 = ff.p0;
-    const uint4 rv = ff.rec[k];
     const int size16 = (int)rv.w;
     const int64_t tableBase = fdp->fixedBase + (int64_t)(p0 * 16) + 64;
     const int64_t dstByte = tableBase + (int64_t)nb * 48 + (int64_t)((pre - p0) * 16);
@@ -96,13 +90,9 @@ __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff
     } else {
         const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)k * kSlotWords);
         uint4 *dst = reinterpret_cast<uint4 *>(p.out + dstByte);
-        for (int c = lane; c < size16; c += 64) {  // two chunks in flight per lane
-            const uint4 v0 = __ldcg(slot + c);
-            uint4 v1 = make_uint4(0u, 0u, 0u, 0u);
-            if (c + 32 < size16) v1 = __ldcg(slot + c + 32);
-            st_stream_u4(dst + c, v0);
-            if (c + 32 < size16) st_stream_u4(dst + c + 32, v1);
-        }
+        if (lane < size16) st_stream_u4(dst + lane, v0);
+        if (lane + 32 < size16) st_stream_u4(dst + lane + 32, v1);
+        for (int c = lane + 64; c < size16; c += 32) st_stream_u4(dst + c, __ldcg(slot + c));
         if (lane == 0) {
             const uint4 e = make_uint4(rv.x, rv.y, rv.z, (uint32_t)(pre - p0));
             *reinterpret_cast<uint4 *>(p.out + tableBase + ((int64_t)comp * nb + b) * 16) = e;
@@ -111,6 +101,29 @@ __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff
     __syncwarp();
     ff.head = (ff.head + 1) % kFifo;
     ff.count--;
+}
+
+// the first two chunks per lane of the oldest parked block
+__device__ __forceinline__ void load_head(const ParkFifo &ff, uint4 &rv, uint4 &v0, uint4 &v1, int lane) {
+    rv = ff.rec[ff.head];
+    const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)ff.head * kSlotWords);
+    v0 = v1 = make_uint4(0u, 0u, 0u, 0u);
+    if (lane < (int)rv.w) v0 = __ldcg(slot + lane);
+    if (lane + 32 < (int)rv.w) v1 = __ldcg(slot + lane + 32);
+}
+
+// place the oldest parked block, waiting for its prefix if need be
+__device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff, int lane) {
+    const int64_t pl = ff.blk[ff.head];
+    uint4 rv, v0, v1;
+    load_head(ff, rv, v0, v1, lane);
+    uint64_t pre = 0;
+    uint32_t spins = 0;
+    while (!block_prefix(p.blkRel, p.winBase, pl, pre)) {
+        __nanosleep(200);
+        if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); return false; }
+    }
+    place_finish(p, ff, pre, rv, v0, v1, lane);
     return true;
 }
 
@@ -122,10 +135,7 @@ template <bool kFromQ>
 __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, float *stage, const RingCtrl &rc,
                                         int s, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
-    // the oldest parked block's prefix is needed late: ask for it first
-    uint64_t preW = 0;
     long long tPh = ff.wst ? clock64() : 0;
-    if (ff.count > 0) preW = peek_prefix(p, ff.blk[ff.head]);
     if (!kFromQ && !(d.flags & kDescQuant) && !wait_quant(p, d)) return false;
     const uint32_t top = (1u << d.depth) - 1u;
     const bool biased = d.depth <= 23;
@@ -187,11 +197,22 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     MNW_PHASE(3)
     if (ff.count == kFifo) {
         if (ff.wst && lane == 0) ff.wst[7] += 1;  // no free slot: the oldest block has to go now
-        if (!place_oldest(p, ff, preW, lane)) return false;
-        preW = 0;
-        if (ff.count > 0) preW = peek_prefix(p, ff.blk[ff.head]);
+        if (!place_oldest(p, ff, lane)) return false;
     }
     MNW_PHASE(4)
+    // ask now for what placing the oldest parked block will need (its prefix, its
+    // first chunks): the loads fly while this block is being parked
+    const bool tryPlace = ff.count > 0;
+    uint32_t relW = 0;
+    uint64_t wbW = 0;
+    uint4 rvH, v0H, v1H;
+    rvH = v0H = v1H = make_uint4(0u, 0u, 0u, 0u);
+    if (tryPlace) {
+        const int64_t hb = ff.blk[ff.head];
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(relW) : "l"(p.blkRel + hb) : "memory");
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(wbW) : "l"(p.winBase + hb / kScanWin) : "memory");
+        load_head(ff, rvH, v0H, v1H, lane);
+    }
     const int k = (ff.head + ff.count) % kFifo;
     uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
     for (int c = lane; c < (int)size16; c += 32) {
@@ -210,15 +231,8 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     ff.count++;
     release_stage(rc, s, true, lane);  // includes __syncwarp
     MNW_PHASE(5)
-    // normally one block out per block in; more only when the parked blocks pile up
-    if (ff.count > 0 && (preW & kPrefixReady)) {
-        if (!place_oldest(p, ff, preW, lane)) return false;
-        while (ff.count > kFifo / 2) {
-            preW = peek_prefix(p, ff.blk[ff.head]);
-            if (!(preW & kPrefixReady)) break;
-            if (!place_oldest(p, ff, preW, lane)) return false;
-        }
-    }
+    if (tryPlace && (relW & kRelReady) && (wbW & kPrefixReady))
+        place_finish(p, ff, (wbW & ~kPrefixReady) + (relW & ~kRelReady), rvH, v0H, v1H, lane);
     MNW_PHASE(6)
     return true;
 }

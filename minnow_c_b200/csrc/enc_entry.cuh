@@ -95,7 +95,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         }
     }
     while (ff.count > 0 && !drain)
-        if (!place_oldest(p, ff, 0, lane)) return;
+        if (!place_oldest(p, ff, lane)) return;
     if (p.stats && lane == 0) {
         atomicAdd(p.stats + 0, (unsigned long long)tA);
         atomicAdd(p.stats + 1, (unsigned long long)tB);
