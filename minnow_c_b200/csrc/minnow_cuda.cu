@@ -6,6 +6,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -82,6 +83,8 @@ struct MnwCudaCtx {
     bool haveLastEnc = false;
     bool timing = false;         // mnwcuda_EnableKernelTiming
     cudaEvent_t ev[10] = {};     // encode: 0..2, decode: 5..8
+    int64_t hostChunkFloats = 64ll << 20;  // raw floats per pipeline chunk of the host-buffer entry points
+    cudaEvent_t pipeEv[6] = {};  // host-buffer pipeline: copied in, kernels done, copied out (two sets each)
     bool evSet[10] = {};
 };
 
@@ -175,6 +178,7 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     ctx->ticket = reinterpret_cast<uint32_t *>(ctx->error) + 16;
     CUDA_CHECK(cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device));
     if (const char *e = getenv("MNWCUDA_ENCODE_LAG")) ctx->encodeLag = atoll(e);
+    if (const char *e = getenv("MNWCUDA_HOST_CHUNK_FLOATS")) ctx->hostChunkFloats = atoll(e) < 1 ? 1 : atoll(e);
     if (const char *e = getenv("MNWCUDA_ENCODE_MARGIN")) ctx->encodeMargin = atoll(e) < 0 ? 0 : atoll(e);
     {
         cudaDriverEntryPointQueryResult qres;
@@ -191,6 +195,7 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
+    for (cudaEvent_t &e : ctx->pipeEv) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     return ctx;
 }
 
@@ -207,6 +212,8 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaStreamDestroy(ctx->copyIn);
     cudaStreamDestroy(ctx->copyOut);
     for (cudaEvent_t e : ctx->ev)
+        if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->pipeEv)
         if (e) cudaEventDestroy(e);
     if (ctx->encStats) {
         unsigned long long h[16];
@@ -655,96 +662,178 @@ extern "C" Field mnwcuda_DecodeField(CField cf, void *buffer) {
 
 // Chunks of fields are staged through device buffers one after another;
 // chunk size is bounded so that scratch stays modest.
+// Host-buffer batches run as a three-stage pipeline over chunks of ~256 MiB of
+// raw floats: copy in (stream copyIn), kernels (stream own), copy out (stream
+// copyOut), two sets of device staging buffers. PCIe is full duplex, so a
+// chunk's copy out overlaps the next chunk's copy in, and the kernels hide
+// behind both. Pinned host buffers make the copies asynchronous; pageable ones
+// work, staged by the driver.
+namespace {
+
+// fields [i, j) of one chunk, re-based to the chunk's staging buffer
+int64_t host_chunk(int64_t limit, const MnwFieldDesc *h_fields, int64_t nFields, int64_t i,
+                   std::vector<MnwFieldDesc> &local, int64_t &floats, int64_t &bound) {
+    local.clear();
+    floats = bound = 0;
+    int64_t j = i;
+    while (j < nFields && (j == i || floats + 3ll * h_fields[j].ParticleLen <= limit)) {
+        MnwFieldDesc d = h_fields[j];
+        d.Offset = floats;
+        floats += 3ll * d.ParticleLen;
+        bound += mnwcuda_FieldBound(d.ParticleLen);
+        local.push_back(d);
+        j++;
+    }
+    return j;
+}
+}  // namespace
+
 extern "C" int64_t mnwcuda_EncodeFieldsHost(MnwCudaCtx *ctx, const float *h_in, const MnwFieldDesc *h_fields,
                                             int64_t nFields, uint8_t *h_out, int64_t outCap,
                                             uint64_t *h_offsets) {
     if (!ctx || nFields < 0) return -1;
     CUDA_CHECK(cudaSetDevice(ctx->device));
-    const int64_t kChunkFloats = 192ll << 20;  // 768 MiB of input per chunk
-    int64_t total = 0, i = 0;
     h_offsets[0] = 0;
-    std::vector<MnwFieldDesc> local;
+    if (nFields == 0) return 0;
+    struct Chunk {
+        int64_t first, end, floats, bound;
+        std::vector<MnwFieldDesc> local;
+    };
+    std::vector<Chunk> chunks;
+    int64_t maxFloats = 0, maxBound = 0, maxCnt = 0;
+    for (int64_t i = 0; i < nFields;) {
+        Chunk c;
+        c.first = i;
+        c.end = host_chunk(ctx->hostChunkFloats, h_fields, nFields, i, c.local, c.floats, c.bound);
+        maxFloats = std::max(maxFloats, c.floats);
+        maxBound = std::max(maxBound, c.bound);
+        maxCnt = std::max(maxCnt, c.end - c.first);
+        i = c.end;
+        chunks.push_back(std::move(c));
+    }
+    // two sets of staging buffers carved out of the three scratch areas
+    const size_t inStride = ((size_t)maxFloats * 4 + 16 + 255) & ~(size_t)255;
+    const size_t outStride = ((size_t)maxBound + 255) & ~(size_t)255;
+    const size_t offStride = ((size_t)(maxCnt + 1) * 8 + 255) & ~(size_t)255;
+    uint8_t *inBuf = static_cast<uint8_t *>(ctx->ioA.need(2 * inStride));
+    uint8_t *outBuf = static_cast<uint8_t *>(ctx->ioB.need(2 * outStride));
+    uint8_t *offBuf = static_cast<uint8_t *>(ctx->ioC.need(2 * offStride));
+    cudaEvent_t *evIn = ctx->pipeEv, *evEnc = ctx->pipeEv + 2, *evOut = ctx->pipeEv + 4;
     std::vector<uint64_t> offs;
-    while (i < nFields) {
-        local.clear();
-        int64_t floats = 0, bound = 0, j = i;
-        while (j < nFields && (j == i || floats + 3ll * h_fields[j].ParticleLen <= kChunkFloats)) {
-            MnwFieldDesc d = h_fields[j];
-            d.Offset = floats;
-            floats += 3ll * d.ParticleLen;
-            bound += mnwcuda_FieldBound(d.ParticleLen);
-            local.push_back(d);
-            j++;
-        }
-        const int64_t cnt = j - i;
-        float *d_in = static_cast<float *>(ctx->ioA.need((size_t)floats * 4 + 16));
-        uint8_t *d_out = static_cast<uint8_t *>(ctx->ioB.need((size_t)bound));
-        uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need((size_t)(cnt + 1) * 8));
-        for (int64_t k = 0; k < cnt; k++) {
-            size_t bytes = (size_t)local[(size_t)k].ParticleLen * 12;
+    int64_t total = 0;
+    int64_t result = 0;
+
+    auto copy_in = [&](size_t c) {
+        const Chunk &ch = chunks[c];
+        float *d_in = reinterpret_cast<float *>(inBuf + (c & 1) * inStride);
+        // the set's previous user (chunk c-2) has been encoded: the host waited for it in its turn
+        for (int64_t k = 0; k < ch.end - ch.first; k++) {
+            const size_t bytes = (size_t)ch.local[(size_t)k].ParticleLen * 12;
             if (bytes)
-                CUDA_CHECK(cudaMemcpyAsync(d_in + local[(size_t)k].Offset, h_in + h_fields[i + k].Offset, bytes,
-                                           cudaMemcpyHostToDevice, ctx->own));
+                CUDA_CHECK(cudaMemcpyAsync(d_in + ch.local[(size_t)k].Offset, h_in + h_fields[ch.first + k].Offset,
+                                           bytes, cudaMemcpyHostToDevice, ctx->copyIn));
         }
-        int rc = mnwcuda_EncodeFieldsDev(ctx, d_in, local.data(), cnt, d_out, bound, d_off, ctx->own);
-        if (rc) return rc;
+        CUDA_CHECK(cudaEventRecord(evIn[c & 1], ctx->copyIn));
+    };
+
+    copy_in(0);
+    for (size_t c = 0; c < chunks.size(); c++) {
+        const Chunk &ch = chunks[c];
+        const int64_t cnt = ch.end - ch.first;
+        const int b = (int)(c & 1);
+        float *d_in = reinterpret_cast<float *>(inBuf + b * inStride);
+        uint8_t *d_out = outBuf + b * outStride;
+        uint64_t *d_off = reinterpret_cast<uint64_t *>(offBuf + b * offStride);
+        CUDA_CHECK(cudaStreamWaitEvent(ctx->own, evIn[b], 0));
+        if (c >= 2) CUDA_CHECK(cudaStreamWaitEvent(ctx->own, evOut[b], 0));  // d_out's previous payload has left
+        int rc = mnwcuda_EncodeFieldsDev(ctx, d_in, ch.local.data(), cnt, d_out, ch.bound, d_off, ctx->own);
+        if (rc) { result = rc; break; }
+        if (c + 1 < chunks.size()) copy_in(c + 1);  // flies while this chunk is encoded and copied out
         offs.resize((size_t)cnt + 1);
         CUDA_CHECK(cudaMemcpyAsync(offs.data(), d_off, (size_t)(cnt + 1) * 8, cudaMemcpyDeviceToHost, ctx->own));
-        int err = mnwcuda_Status(ctx, ctx->own);
-        if (err) return -100 - err;
+        const int err = mnwcuda_Status(ctx, ctx->own);  // waits for this chunk's kernels
+        if (err) { result = -100 - err; break; }
         const int64_t bytes = (int64_t)offs[(size_t)cnt];
-        if (total + bytes > outCap) return -2;
-        CUDA_CHECK(cudaMemcpyAsync(h_out + total, d_out, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->own));
-        CUDA_CHECK(cudaStreamSynchronize(ctx->own));
-        for (int64_t k = 0; k <= cnt; k++) h_offsets[i + k] = (uint64_t)total + offs[(size_t)k];
+        if (total + bytes > outCap) { result = -2; break; }
+        CUDA_CHECK(cudaMemcpyAsync(h_out + total, d_out, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->copyOut));
+        CUDA_CHECK(cudaEventRecord(evOut[b], ctx->copyOut));
+        for (int64_t k = 0; k <= cnt; k++) h_offsets[ch.first + k] = (uint64_t)total + offs[(size_t)k];
         total += bytes;
-        i = j;
     }
-    return total;
+    (void)evEnc;
+    CUDA_CHECK(cudaStreamSynchronize(ctx->copyIn));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->own));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->copyOut));
+    return result ? result : total;
 }
 
 extern "C" int mnwcuda_DecodeFieldsHost(MnwCudaCtx *ctx, const uint8_t *h_in, const uint64_t *h_offsets,
                                         const MnwFieldDesc *h_fields, int64_t nFields, float *h_out) {
     if (!ctx || nFields < 0) return -1;
     CUDA_CHECK(cudaSetDevice(ctx->device));
-    const int64_t kChunkFloats = 192ll << 20;
-    int64_t i = 0;
-    std::vector<MnwFieldDesc> local;
-    std::vector<uint64_t> offs;
-    while (i < nFields) {
-        local.clear();
-        int64_t floats = 0, j = i;
-        while (j < nFields && (j == i || floats + 3ll * h_fields[j].ParticleLen <= kChunkFloats)) {
-            MnwFieldDesc d = h_fields[j];
-            d.Offset = floats;
-            floats += 3ll * d.ParticleLen;
-            local.push_back(d);
-            j++;
-        }
-        const int64_t cnt = j - i;
-        const uint64_t base = h_offsets[i];
-        if (base & 15) return -6;
-        const int64_t bytes = (int64_t)(h_offsets[j] - base);
-        offs.resize((size_t)cnt + 1);
-        for (int64_t k = 0; k <= cnt; k++) offs[(size_t)k] = h_offsets[i + k] - base;
-        uint8_t *d_in = static_cast<uint8_t *>(ctx->ioB.need((size_t)bytes + 16));
-        float *d_out = static_cast<float *>(ctx->ioA.need((size_t)floats * 4 + 16));
-        uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need((size_t)(cnt + 1) * 8));
-        CUDA_CHECK(cudaMemcpyAsync(d_in, h_in + base, (size_t)bytes, cudaMemcpyHostToDevice, ctx->own));
-        CUDA_CHECK(cudaMemcpyAsync(d_off, offs.data(), (size_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, ctx->own));
-        int rc = mnwcuda_DecodeFieldsDev(ctx, d_in, d_off, local.data(), cnt, d_out, ctx->own);
-        if (rc) return rc;
-        for (int64_t k = 0; k < cnt; k++) {
-            size_t nb = (size_t)local[(size_t)k].ParticleLen * 12;
-            if (nb)
-                CUDA_CHECK(cudaMemcpyAsync(h_out + h_fields[i + k].Offset, d_out + local[(size_t)k].Offset, nb,
-                                           cudaMemcpyDeviceToHost, ctx->own));
-        }
-        int err = mnwcuda_Status(ctx, ctx->own);
-        if (err) return -100 - err;
-        i = j;
+    if (nFields == 0) return 0;
+    struct Chunk {
+        int64_t first, end, floats, bytes;
+        std::vector<MnwFieldDesc> local;
+    };
+    std::vector<Chunk> chunks;
+    int64_t maxFloats = 0, maxBytes = 0, maxCnt = 0;
+    for (int64_t i = 0; i < nFields;) {
+        Chunk c;
+        int64_t bound;
+        c.first = i;
+        c.end = host_chunk(ctx->hostChunkFloats, h_fields, nFields, i, c.local, c.floats, bound);
+        if (h_offsets[c.first] & 15) return -6;
+        c.bytes = (int64_t)(h_offsets[c.end] - h_offsets[c.first]);
+        maxFloats = std::max(maxFloats, c.floats);
+        maxBytes = std::max(maxBytes, c.bytes);
+        maxCnt = std::max(maxCnt, c.end - c.first);
+        i = c.end;
+        chunks.push_back(std::move(c));
     }
-    return 0;
+    const size_t inStride = ((size_t)maxBytes + 16 + 255) & ~(size_t)255;
+    const size_t outStride = ((size_t)maxFloats * 4 + 16 + 255) & ~(size_t)255;
+    const size_t offStride = ((size_t)(maxCnt + 1) * 8 + 255) & ~(size_t)255;
+    uint8_t *inBuf = static_cast<uint8_t *>(ctx->ioB.need(2 * inStride));
+    uint8_t *outBuf = static_cast<uint8_t *>(ctx->ioA.need(2 * outStride));
+    uint8_t *offBuf = static_cast<uint8_t *>(ctx->ioC.need(2 * offStride));
+    cudaEvent_t *evIn = ctx->pipeEv, *evDec = ctx->pipeEv + 2, *evOut = ctx->pipeEv + 4;
+    std::vector<uint64_t> offs;
+    int result = 0;
+    for (size_t c = 0; c < chunks.size(); c++) {
+        const Chunk &ch = chunks[c];
+        const int64_t cnt = ch.end - ch.first;
+        const int b = (int)(c & 1);
+        uint8_t *d_in = inBuf + b * inStride;
+        float *d_out = reinterpret_cast<float *>(outBuf + b * outStride);
+        uint64_t *d_off = reinterpret_cast<uint64_t *>(offBuf + b * offStride);
+        const uint64_t base = h_offsets[ch.first];
+        offs.resize((size_t)cnt + 1);
+        for (int64_t k = 0; k <= cnt; k++) offs[(size_t)k] = h_offsets[ch.first + k] - base;
+        if (c >= 2) CUDA_CHECK(cudaStreamWaitEvent(ctx->copyIn, evDec[b], 0));  // the set's previous chunk is decoded
+        // (the small pageable copy first: it is staged synchronously, behind whatever the stream holds)
+        CUDA_CHECK(cudaMemcpyAsync(d_off, offs.data(), (size_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, ctx->copyIn));
+        CUDA_CHECK(cudaMemcpyAsync(d_in, h_in + base, (size_t)ch.bytes, cudaMemcpyHostToDevice, ctx->copyIn));
+        CUDA_CHECK(cudaEventRecord(evIn[b], ctx->copyIn));
+        CUDA_CHECK(cudaStreamWaitEvent(ctx->own, evIn[b], 0));
+        if (c >= 2) CUDA_CHECK(cudaStreamWaitEvent(ctx->own, evOut[b], 0));  // d_out's previous floats have left
+        int rc = mnwcuda_DecodeFieldsDev(ctx, d_in, d_off, ch.local.data(), cnt, d_out, ctx->own);
+        if (rc) { result = rc; break; }
+        CUDA_CHECK(cudaEventRecord(evDec[b], ctx->own));
+        CUDA_CHECK(cudaStreamWaitEvent(ctx->copyOut, evDec[b], 0));
+        for (int64_t k = 0; k < cnt; k++) {
+            const size_t nb = (size_t)ch.local[(size_t)k].ParticleLen * 12;
+            if (nb)
+                CUDA_CHECK(cudaMemcpyAsync(h_out + h_fields[ch.first + k].Offset, d_out + ch.local[(size_t)k].Offset,
+                                           nb, cudaMemcpyDeviceToHost, ctx->copyOut));
+        }
+        CUDA_CHECK(cudaEventRecord(evOut[b], ctx->copyOut));
+    }
+    CUDA_CHECK(cudaStreamSynchronize(ctx->copyIn));
+    const int err = mnwcuda_Status(ctx, ctx->own);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->copyOut));
+    if (result) return result;
+    return err ? -100 - err : 0;
 }
 
 // ---------------------------------------------------------------------------

@@ -141,6 +141,46 @@ def test_host_batch_entry_points(codec):
         assert np.array_equal(back[3 * n * i:3 * n * (i + 1)].view(np.uint32), want.view(np.uint32))
 
 
+def test_host_pipeline_many_chunks(monkeypatch):
+    """The host-buffer entry points as a multi-chunk pipeline (two staging sets,
+    three streams): tiny chunks force 7 chunks of ragged size, with empty fields."""
+    monkeypatch.setenv("MNWCUDA_HOST_CHUNK_FLOATS", str(3 * 5000))
+    c = mc.Codec(0)
+    try:
+        rng = np.random.default_rng(77)
+        sizes = [4097, 100, 0, 2500, 2500, 1, 6000, 1023, 0, 3072, 2048, 777]
+        fields, chunks, off = [], [], 0
+        for i, n in enumerate(sizes):
+            code = mc.FIELD_POSN if i % 2 == 0 else mc.FIELD_VELC
+            if code == mc.FIELD_POSN:
+                x = (rng.uniform(0, 100, (3, 1)) + np.cumsum(rng.normal(0, 0.02, (3, n)), axis=1)) % 100.0
+                delta, width = 1e-3, 100.0
+            else:
+                x = np.cumsum(rng.normal(0, 3.0, (3, n)), axis=1)
+                delta, width = 0.5, 0.0
+            x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+            fields.append((off, n, code, delta, width, 100 + i))
+            chunks.append(x)
+            off += 3 * n
+        flat = np.concatenate(chunks) if off else np.zeros(0, np.float32)
+        descs = mc.make_descs(fields)
+        nf = len(sizes)
+        h_out = np.zeros(sum(mc.field_bound(n) for n in sizes), np.uint8)
+        h_off = np.zeros(nf + 1, np.uint64)
+        total = c.encode_host(flat, descs, nf, h_out, h_off)
+        assert total == int(h_off[nf])
+        for i, (o, n, code, delta, width, seed) in enumerate(fields):
+            want = orc.encode_field(code, chunks[i], delta, width, seed=seed)
+            assert np.array_equal(h_out[int(h_off[i]):int(h_off[i + 1])], want), "field %d" % i
+        back = np.full_like(flat, np.nan)
+        c.decode_host(h_out, h_off, descs, nf, back)
+        for i, (o, n, code, delta, width, seed) in enumerate(fields):
+            want = orc.decode_field(h_out[int(h_off[i]):int(h_off[i + 1])])
+            assert np.array_equal(back[o:o + 3 * n].view(np.uint32), want.view(np.uint32)), "field %d" % i
+    finally:
+        c.close()
+
+
 def test_depth_overflow_is_reported(codec):
     d_in = torch.arange(30, dtype=torch.float32, device="cuda")
     d_out = torch.zeros(mc.field_bound(10), dtype=torch.uint8, device="cuda")
