@@ -83,7 +83,7 @@ struct MnwCudaCtx {
     bool haveLastEnc = false;
     bool timing = false;         // mnwcuda_EnableKernelTiming
     cudaEvent_t ev[10] = {};     // encode: 0..2, decode: 5..8
-    int64_t hostChunkFloats = 64ll << 20;  // raw floats per pipeline chunk of the host-buffer entry points
+    int64_t hostChunkFloats = 32ll << 20;  // raw floats per pipeline chunk of the host-buffer entry points
     cudaEvent_t pipeEv[6] = {};  // host-buffer pipeline: copied in, kernels done, copied out (two sets each)
     bool evSet[10] = {};
 };
@@ -662,7 +662,7 @@ extern "C" Field mnwcuda_DecodeField(CField cf, void *buffer) {
 
 // Chunks of fields are staged through device buffers one after another;
 // chunk size is bounded so that scratch stays modest.
-// Host-buffer batches run as a three-stage pipeline over chunks of ~256 MiB of
+// Host-buffer batches run as a three-stage pipeline over chunks of ~128 MiB of
 // raw floats: copy in (stream copyIn), kernels (stream own), copy out (stream
 // copyOut), two sets of device staging buffers. PCIe is full duplex, so a
 // chunk's copy out overlaps the next chunk's copy in, and the kernels hide
