@@ -6,7 +6,7 @@
 namespace mnw {
 
 // ---------------------------------------------------------------------------
-// k_encode: warp 0 = producer, warps 1..14 = consumers, warp 15 = the scan warp
+// k_encode: warp 0 = producer, warps 1..18 = consumers, warp 19 = the scan warp
 // in CTA 0 and the reduce warp in CTA 1 (the host launches at least two CTAs).
 // ---------------------------------------------------------------------------
 template <bool kFromQ>
@@ -27,7 +27,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     }
     __syncthreads();
     // with enough CTAs the first two do nothing but scan and reduce: a service warp that
-    // shares its SM with 14 busy consumers falls behind, and everybody waits for it
+    // shares its SM with 18 busy consumers falls behind, and everybody waits for it
     const bool service = gridDim.x >= 8 && blockIdx.x < 2;
     if (service && warp != kEncWarps - 1) return;
     if (warp == 0) {
