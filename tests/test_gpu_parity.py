@@ -208,3 +208,44 @@ def test_generator_roundtrip_accuracy(codec):
     err = np.minimum(err, 100.0 - err)
     assert err.max() <= 1e-3 + 2e-5
     assert payload.size < 0.6 * hp.nbytes
+
+
+def test_bench_sized_slab_matches_oracle(codec):
+    """Eight segments of 2^22 particles, positions and velocities (the bench's
+    field size: 4096 blocks per component, every fast path of the persistent
+    encoder) in one batch: every field's bytes against the oracle, twice (the
+    schedule differs from run to run, the bytes must not), and the decoded
+    floats of two fields against the oracle's decoder."""
+    seg, nseg, ngrid = 1 << 22, 8, 512
+    nf = 2 * nseg
+    d_in = torch.empty(nf * 3 * seg, dtype=torch.float32, device="cuda")
+    fields = []
+    for s_ in range(nseg):
+        po, vo = (2 * s_) * 3 * seg, (2 * s_ + 1) * 3 * seg
+        codec.generate(ngrid, 100.0, 4242, s_ * seg, seg, d_in[po:po + 3 * seg], d_in[vo:vo + 3 * seg])
+        fields.append((po, seg, mc.FIELD_POSN, 1e-3, 100.0, 1000 + s_))
+        fields.append((vo, seg, mc.FIELD_VELC, 1.0, 0.0, 2000 + s_))
+    torch.cuda.synchronize()
+    descs = mc.make_descs(fields)
+    d_out = torch.zeros(nf * mc.field_bound(seg), dtype=torch.uint8, device="cuda")
+    d_off = torch.zeros(nf + 1, dtype=torch.int64, device="cuda")
+    codec.encode_dev(d_in, descs, nf, d_out, d_off)
+    assert codec.status() == 0
+    offs = d_off.cpu().numpy()
+    first = d_out[:int(offs[nf])].cpu().numpy().copy()
+    h_in = d_in.cpu().numpy()
+    for i, (o, n, code, delta, width, seed) in enumerate(fields):
+        want = orc.encode_field(code, h_in[o:o + 3 * n], delta, width, seed=seed)
+        assert np.array_equal(first[offs[i]:offs[i + 1]], want), "field %d" % i
+    d_out.zero_()
+    codec.encode_dev(d_in, descs, nf, d_out, d_off)
+    assert codec.status() == 0
+    assert np.array_equal(d_off.cpu().numpy(), offs)
+    assert np.array_equal(d_out[:int(offs[nf])].cpu().numpy(), first)
+    d_dec = torch.zeros_like(d_in)
+    codec.decode_dev(d_out, d_off, descs, nf, d_dec)
+    assert codec.status() == 0
+    for i in (4, 11):
+        o, n = fields[i][0], fields[i][1]
+        want = orc.decode_field(first[offs[i]:offs[i + 1]])
+        assert np.array_equal(d_dec[o:o + 3 * n].cpu().numpy().view(np.uint32), want.view(np.uint32)), "field %d" % i
