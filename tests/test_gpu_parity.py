@@ -249,3 +249,32 @@ def test_bench_sized_slab_matches_oracle(codec):
         o, n = fields[i][0], fields[i][1]
         want = orc.decode_field(first[offs[i]:offs[i + 1]])
         assert np.array_equal(d_dec[o:o + 3 * n].cpu().numpy().view(np.uint32), want.view(np.uint32)), "field %d" % i
+
+
+@pytest.mark.parametrize("depth", list(range(0, 25)))
+def test_depth_sweep_matches_oracle(codec, depth):
+    """BASELINE config 4: the same data at every quantisation depth 0..24 (Delta
+    chosen so that deltaToDepth, src/quant.c:684-688, lands on `depth`), encode
+    bytes and decoded floats against the oracle. Depth 24 takes the encoder's
+    unbiased truncation path, depths <= 23 the biased one."""
+    rng = np.random.default_rng(900 + depth)
+    n = 20000 + 37 * depth
+    x = (50.0 + np.cumsum(rng.normal(0, 0.01, (3, n)), axis=1)) % 100.0
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    # unwrapped range as the encoder sees it (first element anchors the unwrap)
+    span = 0.0
+    for c in range(3):
+        u = x[c].astype(np.float32).copy()
+        rel = u - u[0]
+        u = np.where(rel >= 50.0, u - np.float32(100.0), np.where(rel < -50.0, u + np.float32(100.0), u))
+        span = max(span, float(np.float32(u.max()) - np.float32(u.min())))
+    delta = np.float32(span / 2.0 ** depth * 1.0001) if depth > 0 else np.float32(span * 2)
+    for code, width in ((mc.FIELD_POSN, 100.0), (mc.FIELD_VELC, 0.0)):
+        data = x.reshape(-1)
+        want = orc.encode_field(code, data, float(delta), width, seed=depth)
+        codec.set_dither_seed(depth)
+        got = codec.encode_field(code, data, float(delta), width)
+        assert np.array_equal(got, want), "encode depth %d code %x" % (depth, code)
+        out, _ = codec.decode_field(code, n, got)
+        ref = orc.decode_field(want)
+        assert np.array_equal(out.view(np.uint32), ref.view(np.uint32)), "decode depth %d code %x" % (depth, code)
