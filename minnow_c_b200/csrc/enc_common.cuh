@@ -25,17 +25,20 @@ namespace mnw {
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kEncWarps = 20;        // per CTA (one CTA per SM): producer, 18 consumers, a service warp (scan in CTA 0, reduce in CTA 1)
 constexpr int kEncConsumers = 18;
-constexpr int kEncStages = 48;       // input ring: 4 KiB blocks per SM (TMA, 128-byte swizzle)
+constexpr int kEncStages = 44;       // input ring: 4 KiB blocks per SM (TMA, 128-byte swizzle)
 constexpr int kEncStageBytes = 4096;
 constexpr int kGroupSlots = 32;      // slots per ticket
 constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
-constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 64 + 16 + kEncStages * 4;
+constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 80 + 16 + kEncStages * 4;
 constexpr int kEncFifoOff = kEncCtrlOff + kEncCtrlBytes;   // per consumer: records of its parked blocks
-constexpr int kEncFifoBytes = kEncConsumers * 8 * (16 + 8);
+constexpr int kEncFifoBytes = kEncConsumers * 8 * (16 + 8 + 8);
 constexpr int kEncStatOff = kEncFifoOff + kEncFifoBytes;   // per consumer: 8 phase clocks (MNWCUDA_ENCODE_STATS)
-constexpr int kEncSmemBytes = kEncStatOff + kEncConsumers * 64;
+constexpr int kArenaWords = 512;     // per consumer: packed blocks waiting for their offset, in shared memory
+constexpr int kEncArenaOff = kEncStatOff + kEncConsumers * 64;
+constexpr int kEncSmemBytes = kEncArenaOff + kEncConsumers * kArenaWords * 4;
+static_assert(kEncSmemBytes <= 232448, "k_encode: more shared memory than an SM has");
 constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bits x 1024, 16-byte padded
 
 constexpr uint32_t kAggReady = 0x8000u;       // in a 16-bit size word
@@ -67,6 +70,7 @@ struct EncodeParams {
     uint32_t *blkRel;      // [nBlocks, padded] kRelReady | exclusive prefix within the block's scan window
     uint64_t *winBase;     // [nWin+1] kPrefixReady | exclusive prefix at the window's start; [nWin] = total
     uint32_t *ticket;      // group ticket counter
+    uint4 *tbl;            // [nBlocks] First, MinDelta, Width of the block (k_tables adds Offset16)
     uint64_t *blkMM;       // [nBlocks, padded to kRedWin] ord(min) | ~ord(max) << 32 of the block, 0 = not there yet
     uint64_t *fq;          // [nFields][3][2] published parameters of a component (see publish_quant)
     uint32_t *scratch;     // [CTAs][kEncConsumers][kFifo][kSlotWords] packed blocks waiting for their offset

@@ -33,21 +33,25 @@ __device__ __forceinline__ bool wait_quant(const EncodeParams &p, WorkDesc &d) {
 }
 
 // ---------------------------------------------------------------------------
-// A consumer parks its packed blocks in scratch slots of its own (global memory,
-// L2 resident) and remembers them in a small FIFO; it places the oldest one as
-// soon as that block's prefix has arrived. The warp that wrote a slot is the one
-// that reads it back, lane for lane, so no fences are involved anywhere: the
-// size flags and the prefixes carry their own payload.
+// A consumer parks its packed blocks until their offsets are known and remembers
+// them in a small FIFO; it places the oldest one as soon as that block's prefix
+// has arrived. A block is packed straight into the consumer's arena in shared
+// memory when there is room (a ring allocator, blocks leave in order); otherwise
+// through the ring stage into one of the consumer's scratch slots in global
+// memory (L2 resident). The warp that parked a block is the one that places it,
+// so no fences are involved anywhere: the size flags and the prefixes carry
+// their own payload.
 // ---------------------------------------------------------------------------
 constexpr int kFifo = 8;
 
 struct ParkFifo {
-    uint4 *rec;        // shared: [kFifo] first, minDelta, width, size16
+    int4 *where;       // shared: [kFifo] arena offset in words (-1: scratch slot), arena words taken, packed words, size16
     int64_t *blk;      // shared: [kFifo]
+    int64_t *pay;      // shared: [kFifo] WorkDesc::payBase of the block's field
     uint32_t *slots;   // global: [kFifo][kSlotWords]
+    uint32_t *arena;   // shared: [kArenaWords]
     int head, count;
-    int p0Field;       // field whose first-block prefix is cached in p0, or -1
-    uint64_t p0;
+    int aTail, aUsed;  // arena: next word to hand out, words in use (including skipped tails)
     unsigned long long *wst;  // shared: phase clocks of this warp, or null
 };
 
@@ -58,72 +62,88 @@ struct ParkFifo {
         tPh = tNow_;                                   \
     }
 
+// room for `need` contiguous words in the arena? (-1: no) `span` = words taken, counting a skipped tail
+__device__ __forceinline__ int arena_alloc(ParkFifo &ff, int need, int &span) {
+    int start = ff.aTail, waste = 0;
+    if (start + need > kArenaWords) {
+        waste = kArenaWords - start;
+        start = 0;
+    }
+    span = waste + need;
+    if (need > kArenaWords || ff.aUsed + span > kArenaWords) return -1;
+    ff.aTail = start + need;
+    ff.aUsed += span;
+    return start;
+}
+
 // kPrefixReady | prefix of the block, or 0 if the scan has not got there yet
 __device__ __forceinline__ uint64_t peek_prefix(const EncodeParams &p, int64_t blk) {
     uint64_t pre;
     return block_prefix(p.blkRel, p.winBase, blk, pre) ? (kPrefixReady | pre) : 0ull;
 }
 
-// The oldest parked block goes to its final position: `pre` is its prefix, rv its
-// record, v0/v1 its first two 16-byte chunks per lane (already loaded by the
-// caller so that their latency overlaps other work); wider blocks load the rest here.
-__device__ __forceinline__ void place_finish(const EncodeParams &p, ParkFifo &ff, uint64_t pre, const uint4 &rv,
-                                             const uint4 &v0, const uint4 &v1, int lane) {
+// The oldest parked block goes to its final position: `pre` is its prefix, v0/v1
+// its first two 16-byte chunks per lane if it sits in a scratch slot (loaded by
+// the caller so that their latency overlaps other work; wider blocks load the
+// rest here). Nothing here reads global memory: the table entry was written at
+// packing time (EncodeParams::tbl) and the payload base travelled with the block.
+__device__ __forceinline__ void place_finish(const EncodeParams &p, ParkFifo &ff, uint64_t pre, const uint4 &v0,
+                                             const uint4 &v1, int lane) {
     const int k = ff.head;
-    const int64_t pl = ff.blk[k];
-    int f, comp, b;
-    locate_block(p, pl, f, comp, b);
-    const DevField *fdp = p.fields + f;
-    const int nb = fdp->nb;
-    if (ff.p0Field != f) {  // published no later than `pre`, bar reordering
-        uint64_t p0 = 0;
-        for (uint32_t spins = 0; !block_prefix(p.blkRel, p.winBase, fdp->firstBlock, p0) && spins < kSpinLimit; spins++) {}
-        ff.p0 = p0;
-        ff.p0Field = f;
-    }
-    const uint64_t p0 = ff.p0;
-    const int size16 = (int)rv.w;
-    const int64_t tableBase = fdp->fixedBase + (int64_t)(p0 * 16) + 64;
-    const int64_t dstByte = tableBase + (int64_t)nb * 48 + (int64_t)((pre - p0) * 16);
+    const int4 wh = ff.where[k];
+    const int size16 = wh.w;
+    const int64_t dstByte = ff.pay[k] + (int64_t)(pre * 16);
     if (dstByte + (int64_t)size16 * 16 > p.outCap) {
         if (lane == 0) atomicCAS(p.error, 0, kErrCapacity);
     } else {
-        const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)k * kSlotWords);
         uint4 *dst = reinterpret_cast<uint4 *>(p.out + dstByte);
-        if (lane < size16) st_stream_u4(dst + lane, v0);
-        if (lane + 32 < size16) st_stream_u4(dst + lane + 32, v1);
-        for (int c = lane + 64; c < size16; c += 32) st_stream_u4(dst + c, __ldcg(slot + c));
-        if (lane == 0) {
-            const uint4 e = make_uint4(rv.x, rv.y, rv.z, (uint32_t)(pre - p0));
-            *reinterpret_cast<uint4 *>(p.out + tableBase + ((int64_t)comp * nb + b) * 16) = e;
+        if (wh.x >= 0) {
+            const uint32_t *src = ff.arena + wh.x;
+            const int nWords = wh.z;
+            for (int c = lane; c < size16; c += 32) {
+                const int m = c * 4;
+                uint4 o;
+                o.x = src[skew(m)];
+                o.y = m + 1 < nWords ? src[skew(m + 1)] : 0u;
+                o.z = m + 2 < nWords ? src[skew(m + 2)] : 0u;
+                o.w = m + 3 < nWords ? src[skew(m + 3)] : 0u;
+                st_stream_u4(dst + c, o);
+            }
+        } else {
+            const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)k * kSlotWords);
+            if (lane < size16) st_stream_u4(dst + lane, v0);
+            if (lane + 32 < size16) st_stream_u4(dst + lane + 32, v1);
+            for (int c = lane + 64; c < size16; c += 32) st_stream_u4(dst + c, __ldcg(slot + c));
         }
     }
+    ff.aUsed -= wh.y;
     __syncwarp();
     ff.head = (ff.head + 1) % kFifo;
     ff.count--;
 }
 
-// the first two chunks per lane of the oldest parked block
-__device__ __forceinline__ void load_head(const ParkFifo &ff, uint4 &rv, uint4 &v0, uint4 &v1, int lane) {
-    rv = ff.rec[ff.head];
-    const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)ff.head * kSlotWords);
+// the first two chunks per lane of the oldest parked block (if it sits in a scratch slot)
+__device__ __forceinline__ void load_head(const ParkFifo &ff, uint4 &v0, uint4 &v1, int lane) {
+    const int4 wh = ff.where[ff.head];
     v0 = v1 = make_uint4(0u, 0u, 0u, 0u);
-    if (lane < (int)rv.w) v0 = __ldcg(slot + lane);
-    if (lane + 32 < (int)rv.w) v1 = __ldcg(slot + lane + 32);
+    if (wh.x >= 0) return;
+    const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)ff.head * kSlotWords);
+    if (lane < wh.w) v0 = __ldcg(slot + lane);
+    if (lane + 32 < wh.w) v1 = __ldcg(slot + lane + 32);
 }
 
 // place the oldest parked block, waiting for its prefix if need be
 __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff, int lane) {
     const int64_t pl = ff.blk[ff.head];
-    uint4 rv, v0, v1;
-    load_head(ff, rv, v0, v1, lane);
+    uint4 v0, v1;
+    load_head(ff, v0, v1, lane);
     uint64_t pre = 0;
     uint32_t spins = 0;
     while (!block_prefix(p.blkRel, p.winBase, pl, pre)) {
         __nanosleep(200);
         if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); return false; }
     }
-    place_finish(p, ff, pre, rv, v0, v1, lane);
+    place_finish(p, ff, pre, v0, v1, lane);
     return true;
 }
 
@@ -136,6 +156,16 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
                                         int s, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
     long long tPh = ff.wst ? clock64() : 0;
+    // the oldest parked block's prefix words are asked for now and looked at after
+    // this block is packed: an L2 round trip under load is a few thousand cycles
+    bool tryPlace = ff.count > 0 && ff.count < kFifo;
+    uint32_t relW = 0;
+    uint64_t wbW = 0;
+    if (tryPlace) {
+        const int64_t hb = ff.blk[ff.head];
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(relW) : "l"(p.blkRel + hb) : "memory");
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(wbW) : "l"(p.winBase + hb / kScanWin) : "memory");
+    }
     if (!kFromQ && !(d.flags & kDescQuant) && !wait_quant(p, d)) return false;
     const uint32_t top = (1u << d.depth) - 1u;
     const bool biased = d.depth <= 23;
@@ -184,55 +214,58 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     if (!kFromQ && biased) bs.first -= kQBias;
     const int nWords = (len * bs.w + 31) >> 5;
     const uint32_t size16 = (uint32_t)((nWords + 3) >> 2);
-    // the size is all the scan warp needs: publish it before anything else
+    // the size is all the scan warp needs: publish it before anything else; the
+    // table entry (k_tables adds the offset) goes out with it
+    if (lane == 0) p.tbl[blk] = make_uint4(bs.first, (uint32_t)bs.dmin, (uint32_t)bs.w, 0u);
     if (lane == 0)
         asm volatile("st.relaxed.gpu.global.u16 [%0], %1;" ::"l"(p.blkAgg + blk), "h"((uint16_t)(kAggReady | size16)) : "memory");
 
-    // pack through the block's own stage (its values are in registers by now)
-    uint32_t *tmp = reinterpret_cast<uint32_t *>(stage);
+    if (ff.count == kFifo) {
+        if (ff.wst && lane == 0) ff.wst[7] += 1;  // no free record: the oldest block has to go now
+        if (!place_oldest(p, ff, lane)) return false;
+    }
+    // pack straight into the arena if there is room (the block's values are in
+    // registers by now, so its stage can go back at once), else through the stage
+    int span = 0;
+    // (the pack routines write all 32 x width words of a block, ragged or not)
+    const int loc = arena_alloc(ff, 33 * bs.w + 1, span);
+    uint32_t *tmp = loc >= 0 ? ff.arena + loc : reinterpret_cast<uint32_t *>(stage);
+    if (loc >= 0) release_stage(rc, s, !kFromQ && (d.flags & kDescSlow), lane);  // (a ragged block was staged by hand)
     __syncwarp();
     MNW_PHASE(2)
     if (bs.w > 0) pack_dispatch(bs.w, q, tmp, lane);
     __syncwarp();
     MNW_PHASE(3)
-    if (ff.count == kFifo) {
-        if (ff.wst && lane == 0) ff.wst[7] += 1;  // no free slot: the oldest block has to go now
-        if (!place_oldest(p, ff, lane)) return false;
-    }
     MNW_PHASE(4)
     // ask now for what placing the oldest parked block will need (its prefix, its
-    // first chunks): the loads fly while this block is being parked
-    const bool tryPlace = ff.count > 0;
-    uint32_t relW = 0;
-    uint64_t wbW = 0;
-    uint4 rvH, v0H, v1H;
-    rvH = v0H = v1H = make_uint4(0u, 0u, 0u, 0u);
-    if (tryPlace) {
-        const int64_t hb = ff.blk[ff.head];
-        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(relW) : "l"(p.blkRel + hb) : "memory");
-        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(wbW) : "l"(p.winBase + hb / kScanWin) : "memory");
-        load_head(ff, rvH, v0H, v1H, lane);
-    }
+    // first chunks if they sit in a scratch slot): the loads fly while this block is parked
+    uint4 v0H, v1H;
+    v0H = v1H = make_uint4(0u, 0u, 0u, 0u);
+    if (tryPlace) load_head(ff, v0H, v1H, lane);
     const int k = (ff.head + ff.count) % kFifo;
-    uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
-    for (int c = lane; c < (int)size16; c += 32) {
-        const int m = c * 4;
-        uint4 o;
-        o.x = tmp[skew(m)];
-        o.y = m + 1 < nWords ? tmp[skew(m + 1)] : 0u;
-        o.z = m + 2 < nWords ? tmp[skew(m + 2)] : 0u;
-        o.w = m + 3 < nWords ? tmp[skew(m + 3)] : 0u;
-        slot[c] = o;
+    if (loc < 0) {
+        uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
+        for (int c = lane; c < (int)size16; c += 32) {
+            const int m = c * 4;
+            uint4 o;
+            o.x = tmp[skew(m)];
+            o.y = m + 1 < nWords ? tmp[skew(m + 1)] : 0u;
+            o.z = m + 2 < nWords ? tmp[skew(m + 2)] : 0u;
+            o.w = m + 3 < nWords ? tmp[skew(m + 3)] : 0u;
+            slot[c] = o;
+        }
     }
     if (lane == 0) {
-        ff.rec[k] = make_uint4(bs.first, (uint32_t)bs.dmin, (uint32_t)bs.w, size16);
         ff.blk[k] = blk;
+        ff.pay[k] = d.payBase;
+        ff.where[k] = make_int4(loc, loc >= 0 ? span : 0, nWords, (int)size16);
     }
     ff.count++;
-    release_stage(rc, s, true, lane);  // includes __syncwarp
+    if (loc < 0) release_stage(rc, s, true, lane);  // includes __syncwarp
+    else __syncwarp();
     MNW_PHASE(5)
     if (tryPlace && (relW & kRelReady) && (wbW & kPrefixReady))
-        place_finish(p, ff, (wbW & ~kPrefixReady) + (relW & ~kRelReady), rvH, v0H, v1H, lane);
+        place_finish(p, ff, (wbW & ~kPrefixReady) + (relW & ~kRelReady), v0H, v1H, lane);
     MNW_PHASE(6)
     return true;
 }

@@ -41,12 +41,13 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     }
     const int c = warp - 1;
     ParkFifo ff;
-    ff.rec = reinterpret_cast<uint4 *>(encSmem + kEncFifoOff) + c * kFifo;
+    ff.where = reinterpret_cast<int4 *>(encSmem + kEncFifoOff) + c * kFifo;
     ff.blk = reinterpret_cast<int64_t *>(encSmem + kEncFifoOff + kEncConsumers * kFifo * 16) + c * kFifo;
+    ff.pay = reinterpret_cast<int64_t *>(encSmem + kEncFifoOff + kEncConsumers * kFifo * 24) + c * kFifo;
     ff.slots = p.scratch + ((size_t)blockIdx.x * kEncConsumers + c) * kFifo * kSlotWords;
+    ff.arena = reinterpret_cast<uint32_t *>(encSmem + kEncArenaOff) + c * kArenaWords;
     ff.head = ff.count = 0;
-    ff.p0Field = -1;
-    ff.p0 = 0;
+    ff.aTail = ff.aUsed = 0;
     ff.wst = nullptr;
     if (p.stats) {
         ff.wst = reinterpret_cast<unsigned long long *>(encSmem + kEncStatOff) + c * 8;
@@ -105,6 +106,27 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         atomicAdd(p.stats + 7, (unsigned long long)(clock64() - tStart));
         for (int i = 0; i < 8; i++) atomicAdd(p.stats + 8 + i, ff.wst[i]);
     }
+}
+
+// ---------------------------------------------------------------------------
+// k_tables: one thread per block copies the block's table entry (written at
+// packing time) to its place in the field's block table and adds Offset16, the
+// block's prefix relative to the field's first block.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_tables(EncodeParams p) {
+    const int64_t blk = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (blk >= p.nBlocks) return;
+    int f, comp, b;
+    locate_block(p, blk, f, comp, b);
+    const DevField *fdp = p.fields + f;
+    const int64_t fb = fdp->firstBlock;
+    const uint64_t p0 = (p.winBase[fb / kScanWin] & ~kPrefixReady) + (p.blkRel[fb] & ~kRelReady);
+    const uint64_t pre = (p.winBase[blk / kScanWin] & ~kPrefixReady) + (p.blkRel[blk] & ~kRelReady);
+    const int64_t entry = fdp->fixedBase + (int64_t)(p0 * 16) + 64 + ((int64_t)comp * fdp->nb + b) * 16;
+    if (entry + 16 > p.outCap) { atomicCAS(p.error, 0, kErrCapacity); return; }
+    uint4 e = p.tbl[blk];
+    e.w = (uint32_t)(pre - p0);
+    *reinterpret_cast<uint4 *>(p.out + entry) = e;
 }
 
 // ---------------------------------------------------------------------------

@@ -16,7 +16,7 @@
 
 namespace mnw {
 
-struct WorkDesc {  // 64 bytes, one per ring stage: the block and what its component needs
+struct WorkDesc {  // 80 bytes, one per ring stage: the block and what its component needs
     int32_t kind;
     int32_t f, comp, b;
     int64_t blk;
@@ -28,6 +28,8 @@ struct WorkDesc {  // 64 bytes, one per ring stage: the block and what its compo
     float tHi, tLo;   // unwrap thresholds (kDescPos), see make_unwrap
     float L;
     uint32_t pad;
+    int64_t payBase;  // byte offset of the field's payload area if the batch's prefix were 0
+    int64_t pad2;
 };
 enum : uint32_t {
     kDescSlow = 1u,   // the block did not go through the TMA: the consumer loads it itself
@@ -137,6 +139,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         d.x0 = d.tHi = d.tLo = d.L = 0.0f;
         d.depth = 0;
         d.pad = 0;
+        d.payBase = d.pad2 = 0;
         int64_t blk;
         if (onlyB) {
             blk = g * kGroupSlots + lane;
@@ -156,6 +159,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
             const DevField *fdp = p.fields + d.f;
             const int n = fdp->n;
             d.len = min(kBlockLen, n - d.b * kBlockLen);
+            d.payBase = fdp->fixedBase + 64 + (int64_t)fdp->nb * 48;
             const int64_t off = fdp->ioOff + (int64_t)d.comp * n + (int64_t)d.b * kBlockLen;  // floats from p.in
             row = (p.tmaShift + off) >> 5;
             fast = !kFromQ && p.tmaShift >= 0 && d.len == kBlockLen && ((p.tmaShift + off) & 31) == 0 &&
@@ -206,14 +210,33 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
-        if (use > 0 && !mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4)) return;
-        rc.desc[s] = d;
-        if (fast) {
-            mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
-            tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
-                           (d.kind == kWorkA && (p.dbg & 2)) ? keep : drop);
-        } else {
-            mbar_arrive(rc.full + s);
+        // every lane fills its stage the moment that stage is handed back: a lane must
+        // not wait for the slowest stage of the pass (a B block holds one ten times
+        // longer than an A block)
+        bool filled = false;
+        unsigned long long t0 = 0;
+        for (uint32_t spins = 0;; spins++) {
+            if (!filled && (use == 0 || mbar_try_wait(rc.empty + s, (use - 1) & 1))) {
+                rc.desc[s] = d;
+                if (fast) {
+                    mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
+                    tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
+                                   (d.kind == kWorkA && (p.dbg & 2)) ? keep : drop);
+                } else {
+                    mbar_arrive(rc.full + s);
+                }
+                filled = true;
+            }
+            if (__all_sync(kFull, filled)) break;
+            if ((spins & 1023u) == 1023u) {  // bounded like every other wait
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t0 == 0) t0 = t;
+                else if (t - t0 > 1000000000ull) {
+                    if (!filled) spin_timeout(p.error, 4, -1);
+                    return;
+                }
+            }
         }
         pass++;
     }
@@ -231,6 +254,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         d.scale = 0.0;
         d.x0 = d.tHi = d.tLo = d.L = 0.0f;
         d.depth = d.pad = 0;
+        d.payBase = d.pad2 = 0;
         rc.desc[s] = d;
         mbar_arrive(rc.full + s);
     }

@@ -376,6 +376,7 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     const size_t bWin = ((nWin + 1) * 8 + 15) & ~(size_t)15, bMM = padRed * 8, bFq = nF * 6 * 8;
     const size_t bRel = padScan * 4, bAgg = padScan * 2;
     const size_t stateBytes = bWin + bMM + bFq + bRel + bAgg + 16;
+    p.tbl = static_cast<uint4 *>(ctx->misc.need((size_t)(pl.nBlocks + 1) * sizeof(uint4)));
     uint8_t *st = static_cast<uint8_t *>(ctx->tileState.need(stateBytes));
     p.winBase = reinterpret_cast<uint64_t *>(st);
     p.blkMM = reinterpret_cast<uint64_t *>(st + bWin);
@@ -444,6 +445,10 @@ void launch_finalize(MnwCudaCtx *ctx, const Plan &pl, const EncodeParams &p, cud
     const int nF = (int)pl.fields.size();
     k_finalize<<<(unsigned)((nF + 1 + 127) / 128), 128, 0, s>>>(p, pl.fixedTotal);
     ctx->launches++;
+    if (pl.nBlocks > 0) {
+        k_tables<<<(unsigned)((pl.nBlocks + 255) / 256), 256, 0, s>>>(p);
+        ctx->launches++;
+    }
     CUDA_CHECK(cudaGetLastError());
 }
 
