@@ -221,7 +221,7 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
         asm volatile("st.relaxed.gpu.global.u16 [%0], %1;" ::"l"(p.blkAgg + blk), "h"((uint16_t)(kAggReady | size16)) : "memory");
 
     if (ff.count == kFifo) {
-        if (ff.wst && lane == 0) ff.wst[7] += 1;  // no free record: the oldest block has to go now
+        // no free record: the oldest block has to go now
         if (!place_oldest(p, ff, lane)) return false;
     }
     // pack straight into the arena if there is room (the block's values are in
@@ -230,6 +230,7 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     // (the pack routines write all 32 x width words of a block, ragged or not)
     const int loc = arena_alloc(ff, 33 * bs.w + 1, span);
     uint32_t *tmp = loc >= 0 ? ff.arena + loc : reinterpret_cast<uint32_t *>(stage);
+    if (ff.wst && lane == 0 && loc < 0) ff.wst[7] += 1;  // stats: blocks that went through a scratch slot
     if (loc >= 0) release_stage(rc, s, !kFromQ && (d.flags & kDescSlow), lane);  // (a ragged block was staged by hand)
     __syncwarp();
     MNW_PHASE(2)

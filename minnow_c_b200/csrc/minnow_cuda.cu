@@ -225,7 +225,7 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
                 (double)h[1] / (double)(h[6] ? h[6] : 1), h[5], h[6]);
         const double nB = (double)(h[6] ? h[6] : 1);
         fprintf(stderr, "[mnwcuda encode stats] clk/B-block by phase: params %.0f quantise %.0f delta+width %.0f pack %.0f "
-                        "forced-place %.0f park %.0f place %.0f | forced placements %.1f%%\n",
+                        "wait-free-record %.0f park %.0f place %.0f | through scratch slots %.1f%%\n",
                 h[8] / nB, h[9] / nB, h[10] / nB, h[11] / nB, h[12] / nB, h[13] / nB, h[14] / nB, 100.0 * h[15] / nB);
         cudaFree(ctx->encStats);
     }

@@ -24,7 +24,7 @@ if [ -z "$SKIP_NCU" ]; then
   # launch list of the full-size bench command
   CMD="python bench.py --steps 2 --warmup 1 --no-cpu --no-e2e"
   timeout 600 $CMD > gpurun_out/plain_launch.log 2>&1 &&
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"^k_(encode|finalize|depth_empty|parse_headers|stream_states|unpack_dequant)" -c 60 --csv \
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"^k_(encode|finalize|tables|depth_empty|parse_headers|stream_states|unpack_dequant)" -c 60 --csv \
     --log-file gpurun_out/launches_${TAG}.csv $CMD > gpurun_out/ncu_launch.log 2>&1
   echo "ncu launch list exit $?"; tail -3 gpurun_out/ncu_launch.log
   # DRAM traffic of the two hot kernels at full size (one light pass)
