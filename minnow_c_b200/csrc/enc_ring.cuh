@@ -90,6 +90,13 @@ __device__ __forceinline__ void tma_load_block(void *smemDst, const CUtensorMap 
         "l"(reinterpret_cast<uint64_t>(map)), "r"(0), "r"(row), "r"(smem_u32(bar)), "l"(pol)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_block_plain(void *smemDst, const CUtensorMap *map, int32_t row, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%2, %3}], [%4];" ::"r"(smem_u32(smemDst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(0), "r"(row), "r"(smem_u32(bar))
+        : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
@@ -109,8 +116,9 @@ __device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
 template <bool kFromQ>
 __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMap *map, uint8_t *smem,
                                          const RingCtrl &rc, int lane) {
-    // the A-to-B distance is more than L2 holds next to the parked blocks and the
-    // flag arrays: both reads are streamed (MNWCUDA_DBG=2 keeps the A read instead)
+    // A reads carry no cache hint, B reads are evict_first: with the B work ~56 MB of
+    // A traffic behind, about two thirds of the B reads still hit in L2 (evict_last on
+    // the A reads thrashes: nothing survives; MNWCUDA_DBG=2 tries it, 8 streams both)
     const uint64_t keep = l2_policy_keep(), drop = l2_policy_drop();
     const bool onlyB = kFromQ || p.lagG < 0;
     struct {
@@ -220,8 +228,11 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                 rc.desc[s] = d;
                 if (fast) {
                     mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
-                    tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
-                                   (d.kind == kWorkA && (p.dbg & 2)) ? keep : drop);
+                    if (d.kind == kWorkA && !(p.dbg & 10))
+                        tma_load_block_plain(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s);
+                    else
+                        tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
+                                       (d.kind == kWorkA && (p.dbg & 2)) ? keep : drop);
                 } else {
                     mbar_arrive(rc.full + s);
                 }

@@ -76,7 +76,8 @@ struct MnwCudaCtx {
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     int smCount = 148;
     int64_t encodeLag = -1;      // groups of 16 blocks between the A and B passes (-1: one field + encodeMargin)
-    int64_t encodeMargin = 384;  // groups of slack so that a field's parameters are ready when its B work starts
+    int64_t encodeMargin = 128;  // groups of slack so that a field's parameters are ready when its B work starts
+                                 // (smaller: B work waits for them; larger: its input has left L2 again)
     void *encodeTiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime (no libcuda link)
     unsigned long long *encStats = nullptr;  // MNWCUDA_ENCODE_STATS
     EncodeParams lastEnc;        // most recent encode launch (diagnostics on a device-side timeout)
