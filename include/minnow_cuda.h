@@ -109,7 +109,7 @@ int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx);
 /* Per-kernel device times of the most recent Encode/DecodeFieldsDev call
  * (bench bookkeeping; CUDA events on the call's stream, off by default).
  * ms[0] = k_encode (min/max + quantise + delta + pack, fused), ms[1] =
- * k_finalize, ms[2..3] unused; ms[4..6] = k_parse_headers, k_stream_states,
+ * k_finalize + k_tables, ms[2..3] unused; ms[4..6] = k_parse_headers, k_stream_states,
  * k_unpack_dequant; -1 = not run. */
 void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on);
 int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms /* [7] */);

@@ -259,7 +259,8 @@ class Codec:
     def launches(self):
         return lib().mnwcuda_LaunchCount(self.ctx)
 
-    KERNEL_NAMES = ("k_encode", "k_finalize", "_unused2", "_unused3",
+    # mnwcuda_KernelTimes slots; None = not used by this version of the library
+    KERNEL_NAMES = ("k_encode", "k_finalize+k_tables", None, None,
                     "k_parse_headers", "k_stream_states", "k_unpack_dequant")
 
     def enable_kernel_timing(self, on=True):
@@ -270,7 +271,7 @@ class Codec:
         ms = (C.c_float * 7)()
         if lib().mnwcuda_KernelTimes(self.ctx, ms):
             raise RuntimeError("kernel timing is not enabled")
-        return dict(zip(self.KERNEL_NAMES, [float(v) for v in ms]))
+        return {k: float(v) for k, v in zip(self.KERNEL_NAMES, ms) if k is not None}
 
     # ---- device-resident batch path ----
     def encode_dev(self, d_in, descs, n_fields, d_out, d_offsets, stream=None):
