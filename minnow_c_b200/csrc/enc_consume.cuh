@@ -267,7 +267,7 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     MNW_PHASE(5)
     if (tryPlace && (relW & kRelReady) && (wbW & kPrefixReady))
         place_finish(p, ff, (wbW & ~kPrefixReady) + (relW & ~kRelReady), v0H, v1H, lane);
-    MNW_PHASE(6)
+    MNW_PHASE(5)
     return true;
 }
 

@@ -73,6 +73,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         float *stage = reinterpret_cast<float *>(encSmem + kEncRingOff + s * kEncStageBytes);
         const long long c1 = clock64();
         tQueue += c1 - c0;
+        if (ff.wst && lane == 0 && d.kind == kWorkA) ff.wst[6] += c1 - c0;  // stats: the part spent waiting for A blocks
         if (d.kind == kWorkStop) break;
         if (drain) {  // after a timeout: hand the stages back untouched so that the kernel can end
             release_stage(rc, s, false, lane);

@@ -226,8 +226,9 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
                 (double)h[1] / (double)(h[6] ? h[6] : 1), h[5], h[6]);
         const double nB = (double)(h[6] ? h[6] : 1);
         fprintf(stderr, "[mnwcuda encode stats] clk/B-block by phase: params %.0f quantise %.0f delta+width %.0f pack %.0f "
-                        "wait-free-record %.0f park %.0f place %.0f | through scratch slots %.1f%%\n",
-                h[8] / nB, h[9] / nB, h[10] / nB, h[11] / nB, h[12] / nB, h[13] / nB, h[14] / nB, 100.0 * h[15] / nB);
+                        "wait-free-record %.0f park+place %.0f | through scratch slots %.1f%% | queue time spent on A blocks %.1f%%\n",
+                h[8] / nB, h[9] / nB, h[10] / nB, h[11] / nB, h[12] / nB, h[13] / nB, 100.0 * h[15] / nB,
+                100.0 * (double)h[14] / (double)(h[4] ? h[4] : 1));
         cudaFree(ctx->encStats);
     }
     delete ctx;
