@@ -201,7 +201,7 @@ def cpu_baseline(threads, n_seg, seg, ngrid):
         td = orc.bench_decode(payloads, seg, threads)
         return te, td
 
-    return orc, kind, gen, raw, sum(p.size for p in payloads), one_step
+    return orc, kind, gen, raw, payloads, one_step
 
 
 def run_reference(args):
@@ -212,7 +212,7 @@ def run_reference(args):
     n_seg = args.cpu_segments or max(1, min(threads, 32))
     threads = min(threads, n_seg)
     ngrid = 1024 if args.gpus == 1 else 2048
-    orc, kind, gen, raw, comp, one_step = cpu_baseline(threads, n_seg, SEG, ngrid)
+    orc, kind, gen, raw, _payloads, one_step = cpu_baseline(threads, n_seg, SEG, ngrid)
     for _ in range(args.warmup):
         one_step()
     te = td = 0.0
@@ -402,7 +402,15 @@ def run_b200(args):
 
     cpu = None
     if n_gpus == 1 and not args.no_cpu:
-        cpu = run_cpu_leg(args)
+        offs_h = d_off.cpu().numpy()
+
+        def gpu_payload(i):
+            return d_out[int(offs_h[i]):int(offs_h[i + 1])].cpu().numpy()
+
+        cpu = run_cpu_leg(args, gpu_payload, nf)
+        if cpu.get("parity") is not None:
+            check["sample_bytes_vs_reference"] = cpu["parity"]
+            check["ok"] = bool(check["ok"] and cpu["parity"]["ok"])
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
@@ -526,11 +534,20 @@ def run_e2e(torch, mc, codec, d_in, args, n_gpus, dev, world):
     }
 
 
-def run_cpu_leg(args):
+def run_cpu_leg(args, gpu_payload=None, gpu_fields=0):
+    """The reference's CPU code timed on a bounded sample of the same workload.
+    gpu_payload(i) -> bytes of field i as the GPU arm encoded it: the sample is
+    the slab's first segments, so the two must be byte-identical (SURVEY 8d:
+    parity check in the same run)."""
     threads = os.cpu_count() or 1
     n_seg = args.cpu_segments or max(1, min(threads, 32))
     threads = min(threads, n_seg)
-    orc, kind, gen, raw, comp, one_step = cpu_baseline(threads, n_seg, SEG, 1024)
+    orc, kind, gen, raw, payloads, one_step = cpu_baseline(threads, n_seg, SEG, 1024)
+    parity = None
+    if gpu_payload is not None and gen == "device generator":
+        k = min(len(payloads), gpu_fields)
+        same = sum(1 for i in range(k) if np.array_equal(gpu_payload(i), payloads[i]))
+        parity = {"fields_compared": k, "byte_identical": same, "ok": same == k}
     one_step()
     te = td = 0.0
     reps = 0
@@ -545,6 +562,7 @@ def run_cpu_leg(args):
         "encode_gbs": raw * reps / te / 1e9, "decode_gbs": raw * reps / td / 1e9,
         "sample": "%d segments x 2^%d particles pos+vel (%.0f MiB raw) x %d passes, threads over fields, %s"
                   % (n_seg, SEG_LOG2, raw / 2**20, reps, gen),
+        "parity": parity,
     }
 
 
