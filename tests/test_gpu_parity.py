@@ -278,3 +278,19 @@ def test_depth_sweep_matches_oracle(codec, depth):
         out, _ = codec.decode_field(code, n, got)
         ref = orc.decode_field(want)
         assert np.array_equal(out.view(np.uint32), ref.view(np.uint32)), "decode depth %d code %x" % (depth, code)
+
+
+def test_tiny_range_field_decodes_like_the_oracle(codec):
+    """A field whose bin width is below 2^-100: the decoder's folded dither scale
+    (bw / 2^24) would underflow, so it must take the reference's two-step product."""
+    rng = np.random.default_rng(31)
+    n = 5000
+    x = (rng.uniform(0, 1, 3 * n) * 1e-33).astype(np.float32)
+    delta = float(np.float32(1e-36))
+    want = orc.encode_field(mc.FIELD_VELC, x, delta, 0.0, seed=9)
+    codec.set_dither_seed(9)
+    got = codec.encode_field(mc.FIELD_VELC, x, delta, 0.0)
+    assert np.array_equal(got, want)
+    out, _ = codec.decode_field(mc.FIELD_VELC, n, got)
+    ref = orc.decode_field(want)
+    assert np.array_equal(out.view(np.uint32), ref.view(np.uint32))
