@@ -156,7 +156,7 @@ __device__ __forceinline__ void dequant_block(const uint32_t (&r)[kChunk], uint3
 }
 
 template <bool kToQ>
-__global__ void __launch_bounds__(kDecWarps * 32, 6) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
+__global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
     __shared__ __align__(16) uint32_t stage[kDecWarps][kStageWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t task = (int64_t)blockIdx.x * kDecWarps + warp;
