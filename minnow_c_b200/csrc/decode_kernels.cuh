@@ -130,32 +130,54 @@ __global__ void __launch_bounds__(128) k_stream_states(DecodeParams p) {
 // ---------------------------------------------------------------------------
 constexpr int kDecWarps = 4;
 
-template <bool kGuard>
-__device__ __forceinline__ void dequant_block(const uint32_t (&r)[kChunk], uint32_t base, float x0, float bw,
-                                              bool isPos, float L, int lane, int len, uint64_t &s0,
-                                              uint64_t &s1, float *sf) {
-#pragma unroll
+// The lane's 32 deltas wait in its row of the swizzled staging area (exact floats,
+// |d| < 2^24); S enters as the value before the lane's first one and every
+// partial sum is an integer below 2^24, so the FP32 adds are exact. The loop is
+// rolled (8 values per trip) on purpose: the fully unrolled body was 17 KB of code
+// per variant and the kernel stalled on instruction fetch.
+// kFold: the dither term RN(bits * 2^-24 * bw) is computed as RN((bits * 2^8) *
+// (bw * 2^-32)) -- the same real number rounded once, as long as bw * 2^-32 is
+// itself exact (the caller checks bw >= 2^-90); the shift replaces the 24-bit mask
+// and runs on the FMA pipe. kWrap && isPos: util_Periodic. kGuard: elements at or
+// beyond len draw nothing from the stream (ragged last block).
+template <bool kGuard, bool kWrap, bool kFold, int kRng>
+__device__ __forceinline__ void dequant_row(float S, float x0, float bw, float bwS, bool isPos, float L,
+                                            int lane, int len, uint64_t &s0, uint64_t &s1, float *sf) {
+    uint32_t al = (uint32_t)s0, ah = (uint32_t)(s0 >> 32), bl = (uint32_t)s1, bh = (uint32_t)(s1 >> 32);
+    float4 *row = reinterpret_cast<float4 *>(sf) + lane * 8;
+    const int key = lane & 7;
+#pragma unroll 2
     for (int j = 0; j < 8; j++) {
+        float4 *slot = row + (j ^ key);
+        const float4 d4 = *slot;
+        const float d[4] = {d4.x, d4.y, d4.z, d4.w};
         float o[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const int idx = j * 4 + i;
+            S = __fadd_rn(S, d[i]);
             float v = 0.0f;
-            if (!kGuard || lane * kChunk + idx < len) {
-                uint32_t qv = base + r[idx];
-                float edge = __fadd_rn(x0, __fmul_rn(bw, (float)qv));
-                uint32_t bits = (uint32_t)xs128p_next(s0, s1) & 0xffffffu;
-                float u = __fmul_rn((float)bits, 5.9604644775390625e-08f);  // /2^24, exact
-                v = __fadd_rn(edge, __fmul_rn(u, bw));
-                if (isPos) v = wrap(v, L);
+            if (!kGuard || lane * kChunk + j * 4 + i < len) {
+                float edge = __fadd_rn(x0, __fmul_rn(bw, S));
+                uint32_t sum = xs128p_next32<kRng>(al, ah, bl, bh);
+                float ub;
+                if (kFold) {
+                    ub = __fmul_rn((float)(sum * 256u), bwS);
+                } else {
+                    float u = __fmul_rn((float)(sum & 0xffffffu), 5.9604644775390625e-08f);  // /2^24, exact
+                    ub = __fmul_rn(u, bw);
+                }
+                v = __fadd_rn(edge, ub);
+                if (kWrap && isPos) v = wrap(v, L);
             }
             o[i] = v;
         }
-        reinterpret_cast<float4 *>(sf)[swz_chunk(lane, j)] = make_float4(o[0], o[1], o[2], o[3]);
+        *slot = make_float4(o[0], o[1], o[2], o[3]);
     }
+    s0 = ((uint64_t)ah << 32) | al;
+    s1 = ((uint64_t)bh << 32) | bl;
 }
 
-template <bool kToQ>
+template <bool kToQ, int kRng>
 __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
     __shared__ __align__(16) uint32_t stage[kDecWarps][kStageWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -191,6 +213,8 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
     const bool isPos = fd.fieldCode == field_Posn;
     const float L = qp.width;  // the encoder's box width, not the caller's
     const float bw = __fdiv_rn(qp.maxDiff, (float)(1u << qp.depth));
+    const float bwS = __fmul_rn(bw, 2.3283064365386963e-10f);  // bw * 2^-32
+    const bool foldOK = bw >= 8.0779356694631609e-28f;         // 2^-90: bwS is exact
 
     const int g0 = localTask * kRun;
     const int gCnt = min(3 * fd.nb - g0, kRun);
@@ -225,24 +249,22 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         }
         __syncwarp();
         uint32_t r[kChunk];
-        unpack_dispatch(w, r, st, lane);
-        __syncwarp();
-
-        // ---- inverse delta: inclusive scan of d, d[0] := 0 ----
-        r[0] = lane ? r[0] + minDelta : 0u;
-#pragma unroll
-        for (int i = 1; i < kChunk; i++) r[i] = r[i] + minDelta + r[i - 1];
-        const uint32_t run = r[kChunk - 1];
-        uint32_t incl = run;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += up;
-        }
-        const uint32_t base = first + (incl - run);
 
         if (kToQ) {
-            // literal DFunc boundary: uint64 quantised values out
+            // literal DFunc boundary: integer scan, uint64 quantised values out
+            unpack_dispatch(w, r, st, lane);
+            __syncwarp();
+            r[0] = lane ? r[0] + minDelta : 0u;
+#pragma unroll
+            for (int i = 1; i < kChunk; i++) r[i] = r[i] + minDelta + r[i - 1];
+            const uint32_t run = r[kChunk - 1];
+            uint32_t incl = run;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += up;
+            }
+            const uint32_t base = first + (incl - run);
             uint64_t *dst = p.qOut + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
 #pragma unroll
             for (int i = 0; i < kChunk; i++) st[skew(lane * kChunk + i)] = base + r[i];
@@ -256,13 +278,72 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
             continue;
         }
 
-        // ---- dither + de-quantise + wrap, into swizzled staging ----
-        const float x0 = qp.X0[comp];
+        // ---- deltas as floats, lane totals ----
+        // Residuals of at most 23 bits come out of the unpack as floats 2^23 + r
+        // (bitpack.cuh), and c = minDelta - 2^23 is a float when minDelta >= -2^23:
+        // then d = r + minDelta is one exact FP32 add and the inverse delta needs no
+        // integer pipe at all. Anything else adds in integers and converts (the
+        // deltas of valid data are below 2^24 in magnitude either way).
+        float T = 0.0f;  // sum of the lane's deltas
+        if (w <= 23) unpack_dispatch_magic(w, r, st, lane);
+        else unpack_dispatch_wide(w, r, st, lane);
+        if (w <= 23 && (int32_t)minDelta >= -(1 << 23)) {
+            const float c = __fsub_rn((float)(int32_t)minDelta, 8388608.0f);
+#pragma unroll
+            for (int i = 0; i < kChunk; i++) {
+                float d = __fadd_rn(__uint_as_float(r[i]), c);
+                if (i == 0 && lane == 0) d = 0.0f;  // the block's first value is `first` itself
+                T = __fadd_rn(T, d);
+                r[i] = __float_as_uint(d);
+            }
+        } else {
+            if (w <= 23) {
+#pragma unroll
+                for (int i = 0; i < kChunk; i++) r[i] &= 0x7fffffu;
+            }
+            uint32_t t = 0u;
+#pragma unroll
+            for (int i = 0; i < kChunk; i++) {
+                uint32_t d = r[i] + minDelta;
+                if (i == 0 && lane == 0) d = 0u;
+                t += d;
+                r[i] = __float_as_uint((float)(int32_t)d);
+            }
+            T = (float)(int32_t)t;
+        }
+        __syncwarp();  // everyone has read its packed words: the stage becomes the float area
         float *sf = reinterpret_cast<float *>(st);
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            reinterpret_cast<uint4 *>(sf)[swz_chunk(lane, j)] =
+                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+
+        // ---- inverse delta across lanes: exclusive prefix of the lane totals ----
+        // (taken from the lane below, not as incl - T: the last lane of a ragged
+        // block sums stale words past the payload, and in floating point that does
+        // not cancel)
+        float incl = T;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            float up = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl = __fadd_rn(incl, up);
+        }
+        const float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+        const float basef = lane ? __fadd_rn((float)first, excl) : (float)first;
+
+        // ---- inverse delta within the lane + dither + de-quantise + wrap, in place ----
+        const float x0 = qp.X0[comp];
         float *dst = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
+        if (len == kBlockLen && foldOK) {
+            if (isPos)
+                dequant_row<false, true, true, kRng>(basef, x0, bw, bwS, true, L, lane, len, s0, s1, sf);
+            else
+                dequant_row<false, false, true, kRng>(basef, x0, bw, bwS, false, L, lane, len, s0, s1, sf);
+        } else {
+            dequant_row<true, true, false, kRng>(basef, x0, bw, bwS, isPos, L, lane, len, s0, s1, sf);
+        }
+        __syncwarp();
         if (len == kBlockLen && ((uintptr_t)dst & 15) == 0) {
-            dequant_block<false>(r, base, x0, bw, isPos, L, lane, len, s0, s1, sf);
-            __syncwarp();
 #pragma unroll
             for (int kk = 0; kk < 8; kk++) {
                 int c = kk * 32 + lane;
@@ -270,8 +351,6 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
                 __stcs(reinterpret_cast<float4 *>(dst) + c, v);
             }
         } else {
-            dequant_block<true>(r, base, x0, bw, isPos, L, lane, len, s0, s1, sf);
-            __syncwarp();
 #pragma unroll 4
             for (int kk = 0; kk < 32; kk++) {
                 int el = kk * 32 + lane;

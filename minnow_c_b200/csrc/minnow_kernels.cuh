@@ -86,9 +86,16 @@ __device__ __forceinline__ float unwrap(float v, float anchor, float L, float ha
 
 // util_Periodic's per-element rule (src/util.c:76-82)
 __device__ __forceinline__ float wrap(float v, float L) {
-    if (v >= L) return __fsub_rn(v, L);
-    if (v < 0.0f) return __fadd_rn(v, L);
-    return v;
+    float r = v;  // branch-free: two compares (the second masked by the first), two predicated adds
+    asm("{\n\t"
+        ".reg .pred up, dn;\n\t"
+        "setp.ge.f32 up, %1, %2;\n\t"
+        "setp.lt.and.f32 dn, %1, 0f00000000, !up;\n\t"
+        "@up sub.rn.f32 %0, %1, %2;\n\t"
+        "@dn add.rn.f32 %0, %1, %2;\n\t"
+        "}"
+        : "+f"(r) : "f"(v), "f"(L));
+    return r;
 }
 
 // util_UniformBinIndex's per-element rule (src/util.c:184-191): IEEE division,
@@ -124,6 +131,34 @@ __device__ __forceinline__ uint64_t xs128p_next(uint64_t &s0, uint64_t &s1) {
     b ^= a;
     s0 = ((a << 55) | (a >> 9)) ^ b ^ (b << 14);
     s1 = (b << 36) | (b >> 28);
+    return sum;
+}
+
+// The same step on 32-bit halves (state a = ah:al, b = bh:bl), returning the low
+// word of s0+s1 (rand_Float keeps only its low 24 bits, src/rand.c:60-64). The
+// rotations are written as funnel shifts -- 9 ALU-pipe instructions (4 LOP3, 5 SHF)
+// where the compiler's expansion of the 64-bit form takes 11 -- and b<<14's low
+// word and the sum go to the FMA pipe. kRng = 2 also moves rotr(a,9) there: the
+// two halves of x * 2^23 as a 64-bit product are x<<23 and x>>9.
+template <int kRng>
+__device__ __forceinline__ uint32_t xs128p_next32(uint32_t &al, uint32_t &ah, uint32_t &bl, uint32_t &bh) {
+    const uint32_t sum = al + bl;
+    const uint32_t xl = al ^ bl, xh = ah ^ bh;  // b ^= a
+    uint32_t rl, rh;                            // rotl(a, 55) = rotr(a, 9)
+    if (kRng == 2) {
+        uint64_t u, t;
+        asm("mul.wide.u32 %0, %1, 8388608;" : "=l"(u) : "r"(al));
+        asm("mul.wide.u32 %0, %1, 8388608;" : "=l"(t) : "r"(ah));
+        rl = (uint32_t)(u >> 32) + (uint32_t)t;
+        rh = (uint32_t)(t >> 32) + (uint32_t)u;
+    } else {
+        rl = __funnelshift_r(al, ah, 9);
+        rh = __funnelshift_r(ah, al, 9);
+    }
+    al = rl ^ xl ^ (xl << 14);
+    ah = rh ^ xh ^ __funnelshift_l(xl, xh, 14);
+    bl = __funnelshift_l(xl, xh, 4);  // rotl(b, 36) = rotl(swap halves, 4)
+    bh = __funnelshift_l(xh, xl, 4);
     return sum;
 }
 
