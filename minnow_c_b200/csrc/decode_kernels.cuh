@@ -142,14 +142,12 @@ constexpr int kDecWarps = 4;
 // beyond len draw nothing from the stream (ragged last block).
 template <bool kGuard, bool kWrap, bool kFold, int kRng>
 __device__ __forceinline__ void dequant_row(float S, float x0, float bw, float bwS, bool isPos, float L,
-                                            int lane, int len, uint64_t &s0, uint64_t &s1, float *sf) {
+                                            int lane, int len, uint64_t &s0, uint64_t &s1, uint32_t rowAddr) {
     uint32_t al = (uint32_t)s0, ah = (uint32_t)(s0 >> 32), bl = (uint32_t)s1, bh = (uint32_t)(s1 >> 32);
-    float4 *row = reinterpret_cast<float4 *>(sf) + lane * 8;
-    const int key = lane & 7;
 #pragma unroll 2
     for (int j = 0; j < 8; j++) {
-        float4 *slot = row + (j ^ key);
-        const float4 d4 = *slot;
+        const uint32_t slot = rowAddr ^ (j << 4);
+        const float4 d4 = lds_f4(slot);
         const float d[4] = {d4.x, d4.y, d4.z, d4.w};
         float o[4];
 #pragma unroll
@@ -171,7 +169,7 @@ __device__ __forceinline__ void dequant_row(float S, float x0, float bw, float b
             }
             o[i] = v;
         }
-        *slot = make_float4(o[0], o[1], o[2], o[3]);
+        sts_f4(slot, make_float4(o[0], o[1], o[2], o[3]));
     }
     s0 = ((uint64_t)ah << 32) | al;
     s1 = ((uint64_t)bh << 32) | bl;
@@ -218,24 +216,43 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
 
     const int g0 = localTask * kRun;
     const int gCnt = min(3 * fd.nb - g0, kRun);
+    // Lane i prepares block i of the task once: table entry, component, bounds
+    // check, the component's X0 and whether util_Periodic can do anything to it.
+    // ent.z travels as width | component << 8 | wrap << 10.
     uint4 ent = make_uint4(0u, 0u, 0u, 0u);
-    if (lane < gCnt) ent = __ldg(table + g0 + lane);
-
-    for (int k = 0; k < gCnt; k++) {
-        const int g = g0 + k;
-        const int comp = g / fd.nb;
-        const int b = g - comp * fd.nb;
-        const int len = min(kBlockLen, fd.n - b * kBlockLen);
-        const uint32_t first = __shfl_sync(0xffffffffu, ent.x, k);
-        const uint32_t minDelta = __shfl_sync(0xffffffffu, ent.y, k);
-        const int w = (int)__shfl_sync(0xffffffffu, ent.z, k);
-        const uint32_t off16 = __shfl_sync(0xffffffffu, ent.w, k);
-        const int nWords = (len * w + 31) >> 5;
-        const int size16 = (nWords + 3) >> 2;
-        if (w > kMaxWidth || (int64_t)off16 + size16 > payloadLen16) {
+    float x0L = 0.0f;
+    {
+        bool bad = false;
+        if (lane < gCnt) {
+            ent = __ldg(table + g0 + lane);
+            const int gl = g0 + lane;
+            const int compL = gl / fd.nb;
+            const int lenL = min(kBlockLen, fd.n - (gl - compL * fd.nb) * kBlockLen);
+            const int size16L = (((lenL * (int)ent.z + 31) >> 5) + 3) >> 2;
+            bad = ent.z > (uint32_t)kMaxWidth || (int64_t)ent.w + size16L > payloadLen16;
+            x0L = compL == 0 ? qp.X0[0] : compL == 1 ? qp.X0[1] : qp.X0[2];
+            // every value of the component is x0 + bw*q + dither <= (x0 + maxDiff) + bw
+            // (rounding is monotone), so below L and from 0 up no value is moved
+            const bool inBox = x0L >= 0.0f && __fadd_rn(__fadd_rn(x0L, qp.maxDiff), bw) < L;
+            ent.z |= (uint32_t)compL << 8 | (isPos && !inBox ? 1u << 10 : 0u);
+        }
+        if (__any_sync(0xffffffffu, bad)) {
             if (lane == 0) atomicCAS(p.error, 0, kErrPayload);
             return;
         }
+    }
+    const uint32_t rowAddr = (uint32_t)__cvta_generic_to_shared(st) + lane * 128 + ((lane & 7) << 4);
+
+    for (int k = 0; k < gCnt; k++) {
+        const uint32_t first = __shfl_sync(0xffffffffu, ent.x, k);
+        const uint32_t minDelta = __shfl_sync(0xffffffffu, ent.y, k);
+        const uint32_t zz = __shfl_sync(0xffffffffu, ent.z, k);
+        const uint32_t off16 = __shfl_sync(0xffffffffu, ent.w, k);
+        const int w = (int)(zz & 0xffu);
+        const int comp = (int)(zz >> 8) & 3;
+        const int b = g0 + k - comp * fd.nb;
+        const int len = min(kBlockLen, fd.n - b * kBlockLen);
+        const int size16 = (((len * w + 31) >> 5) + 3) >> 2;
 
         // ---- unpack ----
         const uint4 *src = payload + off16;
@@ -314,9 +331,8 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         __syncwarp();  // everyone has read its packed words: the stage becomes the float area
         float *sf = reinterpret_cast<float *>(st);
 #pragma unroll
-        for (int j = 0; j < 8; j++)
-            reinterpret_cast<uint4 *>(sf)[swz_chunk(lane, j)] =
-                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        for (int j = 0; j < 8; j++)  // chunk j of row `lane` sits at chunk position j ^ (lane & 7)
+            sts_u4(rowAddr ^ (j << 4), make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]));
 
         // ---- inverse delta across lanes: exclusive prefix of the lane totals ----
         // (taken from the lane below, not as incl - T: the last lane of a ragged
@@ -332,24 +348,26 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         const float basef = lane ? __fadd_rn((float)first, excl) : (float)first;
 
         // ---- inverse delta within the lane + dither + de-quantise + wrap, in place ----
-        const float x0 = qp.X0[comp];
+        const float x0 = __shfl_sync(0xffffffffu, x0L, k);
         float *dst = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
         if (len == kBlockLen && foldOK) {
-            if (isPos)
-                dequant_row<false, true, true, kRng>(basef, x0, bw, bwS, true, L, lane, len, s0, s1, sf);
+            if (zz & (1u << 10))
+                dequant_row<false, true, true, kRng>(basef, x0, bw, bwS, true, L, lane, len, s0, s1, rowAddr);
             else
-                dequant_row<false, false, true, kRng>(basef, x0, bw, bwS, false, L, lane, len, s0, s1, sf);
+                dequant_row<false, false, true, kRng>(basef, x0, bw, bwS, false, L, lane, len, s0, s1, rowAddr);
         } else {
-            dequant_row<true, true, false, kRng>(basef, x0, bw, bwS, isPos, L, lane, len, s0, s1, sf);
+            dequant_row<true, true, false, kRng>(basef, x0, bw, bwS, isPos, L, lane, len, s0, s1, rowAddr);
         }
         __syncwarp();
         if (len == kBlockLen && ((uintptr_t)dst & 15) == 0) {
+            // element chunk c = kk*32 + lane lives in row c>>3 at chunk position
+            // (lane&7) ^ (row&7): two base addresses, the rest are immediates
+            const uint32_t r0 = lane >> 3, jj = lane & 7;
+            const uint32_t aEven = (uint32_t)__cvta_generic_to_shared(st) + ((r0 * 8 + (jj ^ r0)) << 4);
+            const uint32_t aOdd = aEven ^ 64u;
+            float4 *d4 = reinterpret_cast<float4 *>(dst) + lane;
 #pragma unroll
-            for (int kk = 0; kk < 8; kk++) {
-                int c = kk * 32 + lane;
-                float4 v = reinterpret_cast<const float4 *>(sf)[swz_chunk(c >> 3, c & 7)];
-                __stcs(reinterpret_cast<float4 *>(dst) + c, v);
-            }
+            for (int kk = 0; kk < 8; kk++) __stcs(d4 + kk * 32, lds_f4(((kk & 1) ? aOdd : aEven) + kk * 512));
         } else {
 #pragma unroll 4
             for (int kk = 0; kk < 32; kk++) {

@@ -140,6 +140,14 @@ __device__ __forceinline__ uint64_t xs128p_next(uint64_t &s0, uint64_t &s1) {
 // where the compiler's expansion of the 64-bit form takes 11 -- and b<<14's low
 // word and the sum go to the FMA pipe. kRng = 2 also moves rotr(a,9) there: the
 // two halves of x * 2^23 as a 64-bit product are x<<23 and x>>9.
+// one LOP3; written out because ptxas otherwise re-associates a ^ (b ^ c) with the
+// xor that produced b and spends an extra instruction
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 template <int kRng>
 __device__ __forceinline__ uint32_t xs128p_next32(uint32_t &al, uint32_t &ah, uint32_t &bl, uint32_t &bh) {
     const uint32_t sum = al + bl;
@@ -155,8 +163,8 @@ __device__ __forceinline__ uint32_t xs128p_next32(uint32_t &al, uint32_t &ah, ui
         rl = __funnelshift_r(al, ah, 9);
         rh = __funnelshift_r(ah, al, 9);
     }
-    al = rl ^ xl ^ (xl << 14);
-    ah = rh ^ xh ^ __funnelshift_l(xl, xh, 14);
+    al = xor3(rl, xl, xl << 14);
+    ah = xor3(rh, xh, __funnelshift_l(xl, xh, 14));
     bl = __funnelshift_l(xl, xh, 4);  // rotl(b, 36) = rotl(swap halves, 4)
     bh = __funnelshift_l(xh, xl, 4);
     return sum;
@@ -170,6 +178,20 @@ __device__ __forceinline__ int skew(int m) { return m + (m >> 5); }
 // staging layout for 32x32 float transposes: 16-byte chunk j of row r sits at
 // chunk position j ^ (r & 7) (the 128-byte XOR swizzle)
 __device__ __forceinline__ int swz_chunk(int row, int j) { return row * 8 + (j ^ (row & 7)); }
+
+// 128-bit shared-memory accesses by 32-bit shared address (the swizzled layouts
+// are walked by XOR on the address)
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts_f4(uint32_t a, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 
 // tile/task -> field lookup: largest f with first[f] <= idx
 template <typename GetFirst>
