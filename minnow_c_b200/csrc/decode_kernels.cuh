@@ -140,7 +140,7 @@ constexpr int kDecWarps = 4;
 // itself exact (the caller checks bw >= 2^-90); the shift replaces the 24-bit mask
 // and runs on the FMA pipe. kWrap && isPos: util_Periodic. kGuard: elements at or
 // beyond len draw nothing from the stream (ragged last block).
-template <bool kGuard, bool kWrap, bool kFold, int kRng>
+template <bool kGuard, bool kWrap, bool kFold>
 __device__ __forceinline__ void dequant_row(float S, float x0, float bw, float bwS, bool isPos, float L,
                                             int lane, int len, uint64_t &s0, uint64_t &s1, uint32_t rowAddr) {
     uint32_t al = (uint32_t)s0, ah = (uint32_t)(s0 >> 32), bl = (uint32_t)s1, bh = (uint32_t)(s1 >> 32);
@@ -156,7 +156,7 @@ __device__ __forceinline__ void dequant_row(float S, float x0, float bw, float b
             float v = 0.0f;
             if (!kGuard || lane * kChunk + j * 4 + i < len) {
                 float edge = __fadd_rn(x0, __fmul_rn(bw, S));
-                uint32_t sum = xs128p_next32<kRng>(al, ah, bl, bh);
+                uint32_t sum = xs128p_next32(al, ah, bl, bh);
                 float ub;
                 if (kFold) {
                     ub = __fmul_rn((float)(sum * 256u), bwS);
@@ -175,7 +175,7 @@ __device__ __forceinline__ void dequant_row(float S, float x0, float bw, float b
     s1 = ((uint64_t)bh << 32) | bl;
 }
 
-template <bool kToQ, int kRng>
+template <bool kToQ>
 __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodeParams p, int64_t nTasksTotal) {
     __shared__ __align__(16) uint32_t stage[kDecWarps][kStageWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -352,11 +352,11 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         float *dst = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
         if (len == kBlockLen && foldOK) {
             if (zz & (1u << 10))
-                dequant_row<false, true, true, kRng>(basef, x0, bw, bwS, true, L, lane, len, s0, s1, rowAddr);
+                dequant_row<false, true, true>(basef, x0, bw, bwS, true, L, lane, len, s0, s1, rowAddr);
             else
-                dequant_row<false, false, true, kRng>(basef, x0, bw, bwS, false, L, lane, len, s0, s1, rowAddr);
+                dequant_row<false, false, true>(basef, x0, bw, bwS, false, L, lane, len, s0, s1, rowAddr);
         } else {
-            dequant_row<true, true, false, kRng>(basef, x0, bw, bwS, isPos, L, lane, len, s0, s1, rowAddr);
+            dequant_row<true, true, false>(basef, x0, bw, bwS, isPos, L, lane, len, s0, s1, rowAddr);
         }
         __syncwarp();
         if (len == kBlockLen && ((uintptr_t)dst & 15) == 0) {

@@ -531,9 +531,7 @@ extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, con
         k_stream_states<<<grid, 128, 0, s>>>(p);
         mark(ctx, 7, s);
         const unsigned dgrid = (unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps);
-        static const int rng = getenv("MNWCUDA_DEC_RNG") ? atoi(getenv("MNWCUDA_DEC_RNG")) : 1;
-        if (rng == 2) k_unpack_dequant<false, 2><<<dgrid, kDecWarps * 32, 0, s>>>(p, pl.nTasks);
-        else k_unpack_dequant<false, 1><<<dgrid, kDecWarps * 32, 0, s>>>(p, pl.nTasks);
+        k_unpack_dequant<false><<<dgrid, kDecWarps * 32, 0, s>>>(p, pl.nTasks);
         mark(ctx, 8, s);
         ctx->launches += 2;
     }
@@ -949,7 +947,7 @@ extern "C" QField MnwCudaDecompress_v0_9(CField cf, void *buffer) {
     k_parse_headers<<<1, 128, 0, s>>>(p);
     ctx->launches++;
     if (pl.nTasks > 0) {
-        k_unpack_dequant<true, 1><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
+        k_unpack_dequant<true><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
             p, pl.nTasks);
         ctx->launches++;
     }

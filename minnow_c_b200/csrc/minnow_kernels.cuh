@@ -138,8 +138,9 @@ __device__ __forceinline__ uint64_t xs128p_next(uint64_t &s0, uint64_t &s1) {
 // word of s0+s1 (rand_Float keeps only its low 24 bits, src/rand.c:60-64). The
 // rotations are written as funnel shifts -- 9 ALU-pipe instructions (4 LOP3, 5 SHF)
 // where the compiler's expansion of the 64-bit form takes 11 -- and b<<14's low
-// word and the sum go to the FMA pipe. kRng = 2 also moves rotr(a,9) there: the
-// two halves of x * 2^23 as a 64-bit product are x<<23 and x>>9.
+// word and the sum go to the FMA pipe. (Moving rotr(a,9) there too, as the halves
+// of the 64-bit product x * 2^23, costs more issue slots than it frees: measured
+// slower.)
 // one LOP3; written out because ptxas otherwise re-associates a ^ (b ^ c) with the
 // xor that produced b and spends an extra instruction
 __device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
@@ -148,21 +149,11 @@ __device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
     return d;
 }
 
-template <int kRng>
 __device__ __forceinline__ uint32_t xs128p_next32(uint32_t &al, uint32_t &ah, uint32_t &bl, uint32_t &bh) {
     const uint32_t sum = al + bl;
-    const uint32_t xl = al ^ bl, xh = ah ^ bh;  // b ^= a
-    uint32_t rl, rh;                            // rotl(a, 55) = rotr(a, 9)
-    if (kRng == 2) {
-        uint64_t u, t;
-        asm("mul.wide.u32 %0, %1, 8388608;" : "=l"(u) : "r"(al));
-        asm("mul.wide.u32 %0, %1, 8388608;" : "=l"(t) : "r"(ah));
-        rl = (uint32_t)(u >> 32) + (uint32_t)t;
-        rh = (uint32_t)(t >> 32) + (uint32_t)u;
-    } else {
-        rl = __funnelshift_r(al, ah, 9);
-        rh = __funnelshift_r(ah, al, 9);
-    }
+    const uint32_t xl = al ^ bl, xh = ah ^ bh;      // b ^= a
+    const uint32_t rl = __funnelshift_r(al, ah, 9);  // rotl(a, 55) = rotr(a, 9)
+    const uint32_t rh = __funnelshift_r(ah, al, 9);
     al = xor3(rl, xl, xl << 14);
     ah = xor3(rh, xh, __funnelshift_l(xl, xh, 14));
     bl = __funnelshift_l(xl, xh, 4);  // rotl(b, 36) = rotl(swap halves, 4)
