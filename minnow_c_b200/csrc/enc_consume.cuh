@@ -28,7 +28,7 @@ __device__ __forceinline__ bool wait_quant(const EncodeParams &p, WorkDesc &d) {
     }
     d.scale = __longlong_as_double((long long)(w0 & ~kFqValid));
     d.x0 = __uint_as_float((uint32_t)w1);
-    d.depth = (uint32_t)(w1 >> 32) & 0x1ffu;
+    d.depth = (uint32_t)(w1 >> 32) & 0xffu;
     return true;
 }
 
@@ -167,8 +167,8 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
         asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(wbW) : "l"(p.winBase + hb / kScanWin) : "memory");
     }
     if (!kFromQ && !(d.flags & kDescQuant) && !wait_quant(p, d)) return false;
-    const uint32_t top = (1u << (d.depth & 0xffu)) - 1u;
-    const bool biased = (d.depth & 0xffu) <= 23;
+    const uint32_t top = (1u << d.depth) - 1u;
+    const bool biased = d.depth <= 23;
     MNW_PHASE(0)
 
     const int len = d.len;
@@ -200,23 +200,12 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
         uw.tHi = d.tHi;
         uw.tLo = d.tLo;
         uw.L = d.L;
-        const bool pos = d.flags & kDescPos;
-        if (d.depth & 0x100u) {  // FP32 quotient (compute_quant chose it): the common case
-            if (biased) {
-                if (pos) quantise32<true, true, true>(stage, lane, uw, d.x0, d.scale, top, q);
-                else quantise32<false, true, true>(stage, lane, uw, d.x0, d.scale, top, q);
-            } else {
-                if (pos) quantise32<true, false, true>(stage, lane, uw, d.x0, d.scale, top, q);
-                else quantise32<false, false, true>(stage, lane, uw, d.x0, d.scale, top, q);
-            }
+        if (d.flags & kDescPos) {
+            if (biased) quantise32<true, true>(stage, lane, uw, d.x0, d.scale, top, q);
+            else quantise32<true, false>(stage, lane, uw, d.x0, d.scale, top, q);
         } else {
-            if (biased) {
-                if (pos) quantise32<true, true, false>(stage, lane, uw, d.x0, d.scale, top, q);
-                else quantise32<false, true, false>(stage, lane, uw, d.x0, d.scale, top, q);
-            } else {
-                if (pos) quantise32<true, false, false>(stage, lane, uw, d.x0, d.scale, top, q);
-                else quantise32<false, false, false>(stage, lane, uw, d.x0, d.scale, top, q);
-            }
+            if (biased) quantise32<false, true>(stage, lane, uw, d.x0, d.scale, top, q);
+            else quantise32<false, false>(stage, lane, uw, d.x0, d.scale, top, q);
         }
     }
 

@@ -59,28 +59,14 @@ __device__ __forceinline__ void compute_quant(const EncodeParams &p, int f) {
     // a constant field has maxDiff = 0: util_UniformBinIndex's 0/0 falls through
     // both clamps and converts to 0 on the host; scale 0 gives the same zeros
     q.scale = md > 0.0f ? __ddiv_rn((double)(1u << depth), (double)md) : 0.0;
-    // With maxDiff well inside the exponent range the quantiser runs in FP32
-    // (quantise32, enc_math.cuh) and `scale` carries its two constants instead:
-    // y = RN_f(2^depth / maxDiff) -- the double quotient rounds to the same float,
-    // a quotient of floats is never that close to a rounding midpoint -- in the low
-    // word and maxDiff * 2^-depth (exact) in the high word. Both are positive, so
-    // the sign bit stays free for kFqValid.
-    q.qmode = 0u;
-    if (md >= 8.67361738e-19f && md <= 1.15292150e18f) {  // 2^-60 .. 2^60
-        const float y = __double2float_rn(q.scale);
-        const float ds = __fmul_rn(md, __uint_as_float((uint32_t)(127 - depth) << 23));
-        q.scale = __longlong_as_double((long long)(((uint64_t)__float_as_uint(ds) << 32) | __float_as_uint(y)));
-        q.qmode = 1u;
-    }
     p.quant[f] = q;
     // what B work needs, as two self-validating words per component: the scale
-    // (a non-negative double: its sign bit is free) and X0 | (depth | qmode << 8) << 32
+    // (a non-negative double: its sign bit is free) and X0 | depth << 32
     if (p.fq) {
         for (int c = 0; c < 3; c++) {
             uint64_t *w = p.fq + ((int64_t)f * 3 + c) * 2;
             const uint64_t w0 = kFqValid | (uint64_t)__double_as_longlong(q.scale);
-            const uint64_t w1 =
-                kFqValid | ((uint64_t)(depth | q.qmode << 8) << 32) | (uint64_t)__float_as_uint(q.X0[c]);
+            const uint64_t w1 = kFqValid | ((uint64_t)depth << 32) | (uint64_t)__float_as_uint(q.X0[c]);
             asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(w), "l"(w0) : "memory");
             asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(w + 1), "l"(w1) : "memory");
         }

@@ -64,22 +64,10 @@ __device__ __forceinline__ float unwrap_t(float v, const Unwrap &u) {
 // bit pattern is kQBias + q; the bias cancels in the deltas. The clamp t >= 1
 // becomes fmin against the largest index (an integer, so trunc commutes).
 // s >= 0 always: x0 is the minimum of the very same unwrapped values.
-//
-// kFma: the scaled quotient s = RN_f(a / maxDiff) * 2^depth = RN_f(a / ds), ds =
-// maxDiff * 2^-depth, by the textbook FMA division with a per-field reciprocal
-// y = RN_f(1/ds) (both in `scale`, see compute_quant): s0 = RN(a*y); twice
-// r = fma(-ds, s, a) (the exact remainder), s = fma(r, y, s). With y correctly
-// rounded and s faithful after the first correction, the second one is correctly
-// rounded (Markstein); compute_quant only selects this mode for 2^-60 <= maxDiff
-// <= 2^60, which keeps every remainder representable wherever the index is not 0
-// anyway. It replaces two conversions on the quarter-rate XU pipe and a DMUL by
-// five FMA-pipe instructions. tests/test_quantiser_exact.py checks the identity.
-template <bool kPos, bool kBiased, bool kFma>
+template <bool kPos, bool kBiased>
 __device__ __forceinline__ void quantise32(const float *stage, int lane, const Unwrap &uw, float x0,
                                            double scale, uint32_t top, uint32_t (&q)[kChunk]) {
     const float topf = (float)top;
-    const float y = __uint_as_float((uint32_t)__double_as_longlong(scale));
-    const float nds = -__uint_as_float((uint32_t)((uint64_t)__double_as_longlong(scale) >> 32));
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         const float4 e4 = reinterpret_cast<const float4 *>(stage)[swz_chunk(lane, j)];
@@ -89,14 +77,7 @@ __device__ __forceinline__ void quantise32(const float *stage, int lane, const U
             float u = e[i];
             if (kPos) u = unwrap_t(u, uw);
             const float a = __fsub_rn(u, x0);
-            float s;
-            if (kFma) {
-                s = __fmul_rn(a, y);
-                s = __fmaf_rn(__fmaf_rn(nds, s, a), y, s);
-                s = __fmaf_rn(__fmaf_rn(nds, s, a), y, s);
-            } else {
-                s = __double2float_rn(__dmul_rn((double)a, scale));
-            }
+            const float s = __double2float_rn(__dmul_rn((double)a, scale));
             if (kBiased) q[j * 4 + i] = __float_as_uint(__fadd_rz(fminf(s, topf), 8388608.0f));
             else q[j * 4 + i] = min(__float2uint_rz(s), top);
         }

@@ -24,7 +24,7 @@ struct WorkDesc {  // 80 bytes, one per ring stage: the block and what its compo
     uint32_t flags;   // kDescSlow | kDescPos | kDescQuant
     double scale;     // util_UniformBinIndex's 2^depth / maxDiff (kDescQuant)
     float x0;
-    uint32_t depth;   // | 1 << 8: scale holds the FMA quantiser's two floats
+    uint32_t depth;
     float tHi, tLo;   // unwrap thresholds (kDescPos), see make_unwrap
     float L;
     uint32_t pad;
@@ -196,14 +196,14 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                     if (w0 & w1 & kFqValid) {
                         pc.scale = __longlong_as_double((long long)(w0 & ~kFqValid));
                         pc.x0 = __uint_as_float((uint32_t)w1);
-                        pc.depth = (uint32_t)(w1 >> 32) & 0x1ffu;
+                        pc.depth = (uint32_t)(w1 >> 32) & 0xffu;
                         pc.flags |= kDescQuant;
                     }
                 } else {
                     const DevQuant *qp = p.quant + d.f;  // given by the caller, written before the launch
                     pc.x0 = __ldg(&qp->X0[d.comp]);
                     pc.scale = __ldg(&qp->scale);
-                    pc.depth = __ldg(&qp->depth) | __ldg(&qp->qmode) << 8;
+                    pc.depth = __ldg(&qp->depth);
                     pc.flags |= kDescQuant;
                 }
             }

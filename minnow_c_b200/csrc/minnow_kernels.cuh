@@ -43,7 +43,6 @@ struct DevQuant {
     float maxDiff;
     uint32_t depth;
     float width;   // decode: box width from the payload header (Posn)
-    uint32_t qmode;  // encode: 1 = `scale` holds the two floats of the FMA quantiser (quant_fma_words)
     double scale;  // encode: RN_double(2^depth / maxDiff), see bin_index_fast
 };
 

@@ -60,21 +60,3 @@ def test_round_toward_zero_add_truncates(depth):
     rz = np.floor(exact).astype(np.float32)
     bits = rz.view(np.uint32)
     np.testing.assert_array_equal(bits - np.uint32(0x4B000000), np.floor(s).astype(np.uint32))
-
-
-def test_fma_quotient_matches_ieee_division(tmp_path):
-    """The encoder's FP32 quantiser (enc_math.cuh quantise32 kFma): FMA division with a
-    per-field reciprocal gives util_UniformBinIndex's index for every value of a
-    field whose maxDiff lies in [2^-60, 2^60] (the range compute_quant selects it for);
-    random values, bin edges, rounding midpoints of the quotient, the top end."""
-    import ctypes
-    import os
-    import subprocess
-    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "quant_fma_check.c")
-    lib = str(tmp_path / "libquantfma.so")
-    subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-shared", "-fPIC", "-o", lib, src, "-lm"])
-    fn = ctypes.CDLL(lib).quant_fma_mismatches
-    fn.restype = ctypes.c_long
-    fn.argtypes = [ctypes.c_uint64, ctypes.c_long, ctypes.c_int, ctypes.c_int, ctypes.c_int]
-    assert fn(1, 200000, 16, -60, 60) == 0
-    assert fn(2, 100000, 16, -4, 12) == 0     # the bench's ranges, more densely
