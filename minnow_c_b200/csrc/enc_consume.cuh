@@ -56,7 +56,7 @@ struct ParkFifo {
 };
 
 #define MNW_PHASE(i)                                   \
-    if (ff.wst) {                                      \
+    if (kStats && ff.wst) {                                    \
         const long long tNow_ = clock64();             \
         if (lane == 0) ff.wst[i] += tNow_ - tPh;       \
         tPh = tNow_;                                   \
@@ -151,11 +151,11 @@ __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff
 // B work on block d.blk
 // ---------------------------------------------------------------------------
 // (false: a wait timed out, the caller leaves the kernel)
-template <bool kFromQ>
+template <bool kFromQ, bool kStats>
 __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, float *stage, const RingCtrl &rc,
                                         int s, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
-    long long tPh = ff.wst ? clock64() : 0;
+    long long tPh = kStats && ff.wst ? clock64() : 0;
     // the oldest parked block's prefix words are asked for now and looked at after
     // this block is packed: an L2 round trip under load is a few thousand cycles
     bool tryPlace = ff.count > 0 && ff.count < kFifo;
@@ -230,7 +230,7 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     // (the pack routines write all 32 x width words of a block, ragged or not)
     const int loc = arena_alloc(ff, 33 * bs.w + 1, span);
     uint32_t *tmp = loc >= 0 ? ff.arena + loc : reinterpret_cast<uint32_t *>(stage);
-    if (ff.wst && lane == 0 && loc < 0) ff.wst[7] += 1;  // stats: blocks that went through a scratch slot
+    if (kStats && ff.wst && lane == 0 && loc < 0) ff.wst[7] += 1;  // stats: blocks that went through a scratch slot
     if (loc >= 0) release_stage(rc, s, !kFromQ && (d.flags & kDescSlow), lane);  // (a ragged block was staged by hand)
     __syncwarp();
     MNW_PHASE(2)

@@ -9,7 +9,10 @@ namespace mnw {
 // k_encode: warp 0 = producer, warps 1..18 = consumers, warp 19 = the scan warp
 // in CTA 0 and the reduce warp in CTA 1 (the host launches at least two CTAs).
 // ---------------------------------------------------------------------------
-template <bool kFromQ>
+// kStats: the per-phase clocks of MNWCUDA_ENCODE_STATS; a separate instantiation so
+// that the normal kernel carries none of the clock reads and 64-bit adds (they were
+// a few per cent of the consumers' instructions).
+template <bool kFromQ, bool kStats>
 __global__ void __launch_bounds__(kEncWarps * 32, 1)
 k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) uint8_t encSmem[];
@@ -49,7 +52,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     ff.head = ff.count = 0;
     ff.aTail = ff.aUsed = 0;
     ff.wst = nullptr;
-    if (p.stats) {
+    if (kStats && p.stats) {
         ff.wst = reinterpret_cast<unsigned long long *>(encSmem + kEncStatOff) + c * 8;
         if (lane == 0)
             for (int i = 0; i < 8; i++) ff.wst[i] = 0;
@@ -57,11 +60,15 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     }
     bool drain = false;
     long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0;
-    const long long tStart = clock64();
+    const long long tStart = kStats ? clock64() : 0;
     while (true) {
-        const long long c0 = clock64();
+        const long long c0 = kStats ? clock64() : 0;
+        // (inline asm: the compiler otherwise wraps the one-lane atomicAdd in its
+        // warp-aggregation sequence, a dozen instructions per claim)
         uint32_t seq = 0;
-        if (lane == 0) seq = atomicAdd(rc.qHead, 1u);
+        if (lane == 0)
+            asm volatile("atom.shared.add.u32 %0, [%1], 1;"
+                         : "=r"(seq) : "r"((uint32_t)__cvta_generic_to_shared(rc.qHead)) : "memory");
         seq = __shfl_sync(kFull, seq, 0);
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
@@ -71,9 +78,11 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         if (!mbar_wait(p.error, rc.full + s, use & 1u, 5)) return;
         WorkDesc d = rc.desc[s];
         float *stage = reinterpret_cast<float *>(encSmem + kEncRingOff + s * kEncStageBytes);
-        const long long c1 = clock64();
-        tQueue += c1 - c0;
-        if (ff.wst && lane == 0 && d.kind == kWorkA) ff.wst[6] += c1 - c0;  // stats: the part spent waiting for A blocks
+        const long long c1 = kStats ? clock64() : 0;
+        if (kStats) {
+            tQueue += c1 - c0;
+            if (ff.wst && lane == 0 && d.kind == kWorkA) ff.wst[6] += c1 - c0;  // stats: the part spent waiting for A blocks
+        }
         if (d.kind == kWorkStop) break;
         if (drain) {  // after a timeout: hand the stages back untouched so that the kernel can end
             release_stage(rc, s, false, lane);
@@ -82,23 +91,27 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         if (d.kind == kWorkA) {
             a_block(p, d, stage, lane);
             release_stage(rc, s, false, lane);
-            tA += clock64() - c1;
-            nA++;
+            if (kStats) {
+                tA += clock64() - c1;
+                nA++;
+            }
         } else if (d.kind == kWorkB) {
-            if (!b_block<kFromQ>(p, d, stage, rc, s, ff, lane)) {
+            if (!b_block<kFromQ, kStats>(p, d, stage, rc, s, ff, lane)) {
                 drain = true;
                 release_stage(rc, s, false, lane);
                 continue;
             }
-            tB += clock64() - c1;
-            nB++;
+            if (kStats) {
+                tB += clock64() - c1;
+                nB++;
+            }
         } else {
             release_stage(rc, s, false, lane);
         }
     }
     while (ff.count > 0 && !drain)
         if (!place_oldest(p, ff, lane)) return;
-    if (p.stats && lane == 0) {
+    if (kStats && p.stats && lane == 0) {
         atomicAdd(p.stats + 0, (unsigned long long)tA);
         atomicAdd(p.stats + 1, (unsigned long long)tB);
         atomicAdd(p.stats + 4, (unsigned long long)tQueue);

@@ -191,8 +191,9 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
         CUDA_CHECK(cudaMalloc(&ctx->encStats, 128));
         CUDA_CHECK(cudaMemset(ctx->encStats, 0, 128));
     }
-    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
-    CUDA_CHECK(cudaFuncSetAttribute(k_encode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -437,8 +438,9 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     if (ctas < 2) ctas = 2;  // the reduce warp lives in CTA 1
     ctx->lastEnc = q;
     ctx->haveLastEnc = true;
-    if (fromQ) k_encode<true><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
-    else k_encode<false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
+    if (fromQ) k_encode<true, false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
+    else if (q.stats) k_encode<false, true><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
+    else k_encode<false, false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
     ctx->launches++;
     CUDA_CHECK(cudaGetLastError());
 }
