@@ -210,7 +210,8 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     }
 
     MNW_PHASE(1)
-    BlockStats bs = delta_width(q, len, lane, p.error);
+    BlockStats bs = (!kFromQ && biased) ? delta_width<true>(q, len, lane, p.error)
+                                        : delta_width<false>(q, len, lane, p.error);
     if (!kFromQ && biased) bs.first -= kQBias;
     const int nWords = (len * bs.w + 31) >> 5;
     const uint32_t size16 = (uint32_t)((nWords + 3) >> 2);

@@ -326,8 +326,23 @@ __device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d
     float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
     if (!(d.flags & kDescSlow)) {
         const float4 *st = reinterpret_cast<const float4 *>(stage);
-        if (isPos) minmax_stage<true>(st, lane, uw, lo, hi);
-        else minmax_stage<false>(st, lane, uw, lo, hi);
+        minmax_stage<false>(st, lane, uw, lo, hi);
+        if (isPos) {
+            // unwrap_t is monotone within each of its three classes (x >= tHi, x < tLo,
+            // between), so if neither threshold separates the lane's raw extrema, the
+            // unwrapped extrema are the unwrapped raw extrema: 1 instruction per value
+            // instead of 5. Rows along y and z almost always qualify; a lane that
+            // straddles a threshold (or holds only NaNs) redoes its values one by one.
+            const bool split = (lo < uw.tHi && !(hi < uw.tHi)) || (lo < uw.tLo && !(hi < uw.tLo)) || !(lo <= hi);
+            if (split) {
+                lo = __int_as_float(0x7f800000);
+                hi = __int_as_float(0xff800000);
+                minmax_stage<true>(st, lane, uw, lo, hi);
+            } else {
+                lo = unwrap_t(lo, uw);
+                hi = unwrap_t(hi, uw);
+            }
+        }
     } else {
         const DevField *fdp = p.fields + d.f;
         const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;

@@ -91,12 +91,34 @@ struct BlockStats {
 
 // delta along the block, min/max over j in [1, len), width; leaves the
 // residuals r[j] = d[j] - dmin in q (r[0] = 0, zeros beyond len)
+// kBiasedQ: q holds the bit patterns of the floats 2^23 + index (quantise32's
+// kBiased form). Their differences are exact in FP32, so for a full block the
+// first pass runs on the FMA pipe with three-input min/max (FMNMX3; there is no
+// integer counterpart on sm_100): 64 instructions instead of 96.
+template <bool kBiasedQ>
 __device__ __forceinline__ BlockStats delta_width(uint32_t (&q)[kChunk], int len, int lane, int *error) {
     const uint32_t prevLast = __shfl_up_sync(kFull, q[kChunk - 1], 1);
     BlockStats bs;
     bs.first = __shfl_sync(kFull, q[0], 0);
     int dmin, dmax;
-    if (len == kBlockLen) {
+    if (kBiasedQ && len == kBlockLen) {
+        float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+        if (lane) lo = hi = __fsub_rn(__uint_as_float(q[0]), __uint_as_float(prevLast));
+        {
+            const float d = __fsub_rn(__uint_as_float(q[1]), __uint_as_float(q[0]));
+            lo = fminf(lo, d);
+            hi = fmaxf(hi, d);
+        }
+#pragma unroll
+        for (int i = 2; i < kChunk; i += 2) {
+            const float d0 = __fsub_rn(__uint_as_float(q[i]), __uint_as_float(q[i - 1]));
+            const float d1 = __fsub_rn(__uint_as_float(q[i + 1]), __uint_as_float(q[i]));
+            lo = fminf(lo, fminf(d0, d1));
+            hi = fmaxf(hi, fmaxf(d0, d1));
+        }
+        dmin = __float2int_rn(lo);
+        dmax = __float2int_rn(hi);
+    } else if (len == kBlockLen) {
         const int d0 = (int)(q[0] - prevLast);
         dmin = lane ? d0 : INT32_MAX;
         dmax = lane ? d0 : INT32_MIN;
