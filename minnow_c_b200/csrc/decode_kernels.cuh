@@ -231,9 +231,15 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
             const int size16L = (((lenL * (int)ent.z + 31) >> 5) + 3) >> 2;
             bad = ent.z > (uint32_t)kMaxWidth || (int64_t)ent.w + size16L > payloadLen16;
             x0L = compL == 0 ? qp.X0[0] : compL == 1 ? qp.X0[1] : qp.X0[2];
-            // every value of the component is x0 + bw*q + dither <= (x0 + maxDiff) + bw
-            // (rounding is monotone), so below L and from 0 up no value is moved
-            const bool inBox = x0L >= 0.0f && __fadd_rn(__fadd_rn(x0L, qp.maxDiff), bw) < L;
+            // Can util_Periodic move any value of this component? The values are
+            // x0 + bw*q + dither with q up to the index of X1 (the component's own
+            // maximum), i.e. at most X1 + bw plus a few roundings of relative size
+            // 2^-24 -- covered by one more bw and 2^-20 of the bound; from below they
+            // cannot get under x0 (rounding is monotone). Inside [0, L) nothing moves.
+            const float x1L = compL == 0 ? qp.X1[0] : compL == 1 ? qp.X1[1] : qp.X1[2];
+            float top = __fadd_rn(x1L, __fadd_rn(bw, bw));
+            top = __fadd_rn(top, __fmul_rn(fabsf(top), 9.5367431640625e-07f));
+            const bool inBox = x0L >= 0.0f && top < L;
             ent.z |= (uint32_t)compL << 8 | (isPos && !inBox ? 1u << 10 : 0u);
         }
         if (__any_sync(0xffffffffu, bad)) {
