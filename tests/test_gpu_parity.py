@@ -38,6 +38,26 @@ def cases():
     rng = np.random.default_rng(5)
     yield "wide_vel", mc.FIELD_VELC, (rng.standard_normal(3 * 70000) * 500).astype(np.float32), 1e-3, 0.0
     yield "negzero", mc.FIELD_VELC, np.array([-0.0, 0.0, 1.0] * 3, np.float32), 0.1, 0.0
+    # the decoder skips util_Periodic for components that cannot leave [0, L): one
+    # component hugging the top of the box (dither carries values past L), one at the
+    # bottom, one well inside, planar x | y | z
+    n = 5000
+    r = np.random.default_rng(9)
+    L = np.float32(10.0)
+    x = (L - np.float32(1e-6) - r.uniform(0, 0.02, n).astype(np.float32)).astype(np.float32)
+    y = r.uniform(0, 0.02, n).astype(np.float32)
+    y[0] = 0.0
+    z = r.uniform(4.0, 4.5, n).astype(np.float32)
+    yield "box_edges", mc.FIELD_POSN, np.concatenate([x, y, z]), 1e-3, float(L)
+    yield "box_edges_coarse", mc.FIELD_POSN, np.concatenate([x, y, z]), 0.3, float(L)
+    # alternating extremes at depth 24: deltas near +-2^24, width 25, minDelta < -2^23
+    # (the decoder's integer scan instead of the FP32 one)
+    v = np.where(np.arange(3 * 3000) % 2 == 0, 0.0, 1000.0).astype(np.float32)
+    v[7::11] = 333.25
+    yield "alternating_depth24", mc.FIELD_VELC, v, 1000.0 / 2**24 * 1.0001, 0.0
+    # width 0 with minDelta < -2^23 (two values, top of the range then bottom): FP32
+    # unpack, integer scan
+    yield "deep_drop_depth24", mc.FIELD_VELC, np.array([900.0, 0.0] * 3, np.float32), 900.0 / 2**24 * 1.0001, 0.0
 
 
 CASES = list(cases())
