@@ -435,6 +435,8 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     // one persistent CTA per SM; fewer when the batch is tiny
     int64_t ctas = q.nGroups * kGroupSlots / kEncConsumers + 1;
     if (ctas > ctx->smCount) ctas = ctx->smCount;
+    if (const char *e = getenv("MNWCUDA_ENCODE_CTAS"))  // debugging: does the time scale with the SMs?
+        if (atoi(e) >= 8 && atoi(e) < ctas) ctas = atoi(e);
     if (ctas < 2) ctas = 2;  // the reduce warp lives in CTA 1
     ctx->lastEnc = q;
     ctx->haveLastEnc = true;
