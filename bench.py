@@ -111,22 +111,32 @@ class Clocks:
 # ---------------------------------------------------------------------------
 # workload
 # ---------------------------------------------------------------------------
-def field_list(n_segments, seg=SEG):
+FIELD_POSN, FIELD_VELC = 0x506F736E, 0x56656C63
+
+
+def field_seed(i, first_field=0):
+    """Dither seed of field i of the snapshot: every field its own (the reference
+    seeds every undoFloat call afresh, /root/reference/src/quant.c:639)."""
+    return 0x5EED0000 + first_field + i
+
+
+def field_list(n_segments, seg=SEG, first_field=0, same_seed=False):
     """[(float offset, n, code, delta, width, seed)]: field 2s = positions of
     segment s, 2s+1 = velocities; each 3*seg planar floats."""
-    import minnow_c_b200 as mc
     out = []
     for s in range(n_segments):
-        out.append(((2 * s) * 3 * seg, seg, mc.FIELD_POSN, POS_DELTA, BOX, 0))
-        out.append(((2 * s + 1) * 3 * seg, seg, mc.FIELD_VELC, VEL_DELTA, 0.0, 0))
+        sp = 0 if same_seed else field_seed(2 * s, first_field)
+        sv = 0 if same_seed else field_seed(2 * s + 1, first_field)
+        out.append(((2 * s) * 3 * seg, seg, FIELD_POSN, POS_DELTA, BOX, sp))
+        out.append(((2 * s + 1) * 3 * seg, seg, FIELD_VELC, VEL_DELTA, 0.0, sv))
     return out
 
 
-def generate(codec, d_in, ngrid, first_id, n_segments, seg=SEG):
+def generate(codec, d_in, ngrid, first_id, n_segments, seg=SEG, noise_cells=0.0):
     for s in range(n_segments):
         pos = d_in[(2 * s) * 3 * seg:(2 * s + 1) * 3 * seg]
         vel = d_in[(2 * s + 1) * 3 * seg:(2 * s + 2) * 3 * seg]
-        codec.generate(ngrid, BOX, GEN_SEED, first_id + s * seg, seg, pos, vel)
+        codec.generate(ngrid, BOX, GEN_SEED, first_id + s * seg, seg, pos, vel, noise_cells=noise_cells)
 
 
 def peaks():
@@ -150,58 +160,63 @@ def load_oracle():
     return _oracle.port(), "port"
 
 
-def host_sample(n_fields_half, seg, ngrid):
-    """n_fields_half segments of pos+vel as host arrays. Uses the device
-    generator when a GPU is present (the same floats as the GPU arm), else the
-    numpy twin of tests/_data.py."""
-    try:
-        import torch
-        have_gpu = torch.cuda.is_available()
-    except Exception:
-        have_gpu = False
-    if have_gpu:
-        import torch
-        import minnow_c_b200 as mc
-        codec = mc.Codec(0)
-        d = torch.empty(n_fields_half * 6 * seg, dtype=torch.float32, device="cuda:0")
-        generate(codec, d, ngrid, 0, n_fields_half, seg)
-        torch.cuda.synchronize()
-        h = d.cpu().numpy()
-        codec.close()
-        del d
-        return h, "device generator"
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from _data import zeldovich_host
-    chunks = []
-    for s in range(n_fields_half):
-        pos, vel = zeldovich_host(ngrid, L=BOX, seed=GEN_SEED % 65536, start=s * seg, count=seg)
-        chunks += [pos.reshape(-1), (2.0 * vel).reshape(-1)]
-    return np.concatenate(chunks), "numpy twin"
-
-
-def cpu_baseline(threads, n_seg, seg, ngrid):
-    orc, kind = load_oracle()
-    FIELD_POSN, FIELD_VELC = 0x506F736E, 0x56656C63
-    h, gen = host_sample(n_seg, seg, ngrid)
-    fl = h.reshape(n_seg, 2, 3 * seg)
-    pos = np.ascontiguousarray(fl[:, 0, :]).reshape(-1)
-    vel = np.ascontiguousarray(fl[:, 1, :]).reshape(-1)
-    del h, fl
-    payloads = []
+def host_sample(orc, n_seg, seg, ngrid, threads):
+    """n_seg segments of pos+vel made on the host by the oracle's generator (the
+    device generator's recipe on host libm): the reference arm never loads the
+    CUDA library. Returns (pos[n_seg*3*seg], vel[...])."""
+    pos = np.empty(n_seg * 3 * seg, np.float32)
+    vel = np.empty(n_seg * 3 * seg, np.float32)
     for s in range(n_seg):
-        payloads.append(orc.encode_field(FIELD_POSN, pos[s * 3 * seg:(s + 1) * 3 * seg], POS_DELTA, BOX))
-        payloads.append(orc.encode_field(FIELD_VELC, vel[s * 3 * seg:(s + 1) * 3 * seg], VEL_DELTA, 0.0))
+        p, v = orc.gen_zeldovich(ngrid, BOX, GEN_SEED, s * seg, seg, 0.0, threads)
+        pos[s * 3 * seg:(s + 1) * 3 * seg] = p
+        vel[s * 3 * seg:(s + 1) * 3 * seg] = v
+    return pos, vel
+
+
+def cpu_baseline(orc, pos, vel, threads, n_seg, seg, seeds=None):
+    """Stepper over a host sample: one step = encode + decode of n_seg pos fields
+    and n_seg vel fields, independent fields spread over `threads` host threads."""
+    payloads = []
+    if seeds is None:
+        seeds = [field_seed(i) for i in range(2 * n_seg)]
+    for s in range(n_seg):
+        payloads.append(orc.encode_field(FIELD_POSN, pos[s * 3 * seg:(s + 1) * 3 * seg], POS_DELTA, BOX,
+                                         seed=seeds[2 * s]))
+        payloads.append(orc.encode_field(FIELD_VELC, vel[s * 3 * seg:(s + 1) * 3 * seg], VEL_DELTA, 0.0,
+                                         seed=seeds[2 * s + 1]))
     raw = 2 * n_seg * 3 * seg * 4
 
-    def one_step():
+    def one_step(o=orc, nthreads=threads, k=n_seg):
         te = 0.0
         for code, data, delta, width in ((FIELD_POSN, pos, POS_DELTA, BOX), (FIELD_VELC, vel, VEL_DELTA, 0.0)):
-            secs, _ = orc.bench_encode(code, data, seg, n_seg, delta, width, threads)
+            secs, _ = o.bench_encode(code, data[:k * 3 * seg], seg, k, delta, width, nthreads)
             te += secs
-        td = orc.bench_decode(payloads, seg, threads)
+        td = o.bench_decode(payloads[:2 * k], seg, nthreads)
         return te, td
 
-    return orc, kind, gen, raw, payloads, one_step
+    return raw, payloads, one_step
+
+
+def extra_cpu_figures(orc, one_step, seg):
+    """The two other figures BASELINE.md section 4 promises: 1 thread (what the
+    reference can do by itself: it has no threads) and the -D DEBUG build its own
+    Makefile ships (Makefile:13-15), on a 1-segment sample."""
+    out = {}
+    raw1 = 2 * 3 * seg * 4
+    te, td = one_step(orc, 1, 1)
+    out["threads1_gbs"] = 2 * raw1 / (te + td) / 1e9
+    out["threads1_encode_gbs"] = raw1 / te / 1e9
+    out["threads1_decode_gbs"] = raw1 / td / 1e9
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle
+    dbg = _oracle.reference_debug()
+    if dbg is not None:
+        te, td = one_step(dbg, 1, 1)
+        out["debug_gbs"] = 2 * raw1 / (te + td) / 1e9
+        out["debug_note"] = "reference compiled -D DEBUG (its Makefile's flags), 1 thread, 1 segment"
+    else:
+        out["debug_gbs"] = None
+    return out
 
 
 def run_reference(args):
@@ -212,7 +227,9 @@ def run_reference(args):
     n_seg = args.cpu_segments or max(1, min(threads, 32))
     threads = min(threads, n_seg)
     ngrid = 1024 if args.gpus == 1 else 2048
-    orc, kind, gen, raw, _payloads, one_step = cpu_baseline(threads, n_seg, SEG, ngrid)
+    orc, kind = load_oracle()
+    pos, vel = host_sample(orc, n_seg, SEG, ngrid, os.cpu_count() or 1)
+    raw, _payloads, one_step = cpu_baseline(orc, pos, vel, threads, n_seg, SEG)
     for _ in range(args.warmup):
         one_step()
     te = td = 0.0
@@ -223,15 +240,18 @@ def run_reference(args):
         td += b
     wall = time.perf_counter() - t0
     value = 2 * raw * args.steps / (te + td) / 1e9
-    sample = ("%d segments x 2^%d particles, pos+vel (%.0f MiB raw) per step, %s; encode %.3f GB/s, decode %.3f GB/s"
-              % (n_seg, SEG_LOG2, raw / 2**20, gen, raw * args.steps / te / 1e9, raw * args.steps / td / 1e9))
+    sample = ("%d segments x 2^%d particles, pos+vel (%.0f MiB raw) per step, host generator (oracle); "
+              "encode %.3f GB/s, decode %.3f GB/s"
+              % (n_seg, SEG_LOG2, raw / 2**20, raw * args.steps / te / 1e9, raw * args.steps / td / 1e9))
+    base = {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample}
+    base.update(extra_cpu_figures(orc, one_step, SEG))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * (te + td) / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32/u32",
         "data": "synthetic",
         "config": workload_config(args.gpus, sample_only=True),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "cpu_baseline": base,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": wall,
     }
@@ -279,7 +299,7 @@ def run_b200(args):
     ngrid = 1024 if n_gpus == 1 else 2048
     first_id = rank * n_seg * seg
     codec = mc.Codec(local)
-    fields = field_list(n_seg, seg)
+    fields = field_list(n_seg, seg, first_field=rank * 2 * n_seg, same_seed=args.same_seed)
     nf = len(fields)
     descs = mc.make_descs(fields)
     raw_bytes = nf * 3 * seg * 4
@@ -367,6 +387,9 @@ def run_b200(args):
     gather = None
     if world > 1 and not args.no_gather:
         gather = run_gather(torch, dist, sharded, d_out, d_off, nf, dev, rank)
+    shard_parity = None
+    if world > 1 and not args.no_cpu:
+        shard_parity = sharded_parity(torch, dist, d_in, d_out, d_off, fields, dev, pick=(0, 1, nf - 2, nf - 1))
 
     value = n_gpus * 2 * raw_bytes * args.steps / (tot_ms * 1e-3) / 1e9
     enc_gbs = n_gpus * raw_bytes * args.steps / (enc_ms * 1e-3) / 1e9
@@ -407,10 +430,17 @@ def run_b200(args):
         def gpu_payload(i):
             return d_out[int(offs_h[i]):int(offs_h[i + 1])].cpu().numpy()
 
-        cpu = run_cpu_leg(args, gpu_payload, nf)
+        cpu = run_cpu_leg(args, d_in, fields, gpu_payload, nf)
         if cpu.get("parity") is not None:
             check["sample_bytes_vs_reference"] = cpu["parity"]
             check["ok"] = bool(check["ok"] and cpu["parity"]["ok"])
+    if shard_parity is not None:
+        check["sample_bytes_vs_reference"] = shard_parity
+        check["ok"] = bool(check["ok"] and shard_parity["ok"])
+
+    sweep = None
+    if n_gpus == 1 and not args.no_sweep:
+        sweep = run_sweep(torch, mc, codec, d_in, d_out, d_off, d_dec, fields, seg, peak, ngrid, first_id, n_seg)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
@@ -427,6 +457,8 @@ def run_b200(args):
     }
     if gather is not None:
         line["gather"] = gather
+    if sweep is not None:
+        line["sweep"] = sweep
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -491,7 +523,7 @@ def run_e2e(torch, mc, codec, d_in, args, n_gpus, dev, world):
     import torch.distributed as dist
     n_seg = min(args.e2e_segments, args.segments)
     seg = SEG
-    fields = field_list(n_seg, seg)
+    fields = field_list(n_seg, seg, same_seed=args.same_seed)
     nf = len(fields)
     descs = mc.make_descs(fields)
     floats = nf * 3 * seg
@@ -524,30 +556,47 @@ def run_e2e(torch, mc, codec, d_in, args, n_gpus, dev, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     elapsed, te, td = [float(v) for v in t.cpu()]
     raw = floats * 4
+    # the ceiling: the same bytes over the same pinned buffers with no kernels, all ranks at once
+    if world > 1:
+        dist.barrier()
+    tc = torch.tensor([host_ceiling(torch, h_in, h_out, dev, raw, int(total))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tc, op=dist.ReduceOp.MAX)
+    ceiling = n_gpus * 2 * raw / float(tc.item()) / 1e9
+    value = n_gpus * 2 * raw * steps / elapsed / 1e9
     return {
-        "value": n_gpus * 2 * raw * steps / elapsed / 1e9, "unit": UNIT,
+        "value": value, "unit": UNIT,
         "h2d_bytes_per_step": int(raw + total), "d2h_bytes_per_step": int(total + raw),
         "encode_gbs": n_gpus * raw * steps / te / 1e9, "decode_gbs": n_gpus * raw * steps / td / 1e9,
+        "host_ceiling_gbs": ceiling, "frac_of_ceiling": value / ceiling,
+        "host_ceiling_note": "copies only (H2D raw || D2H packed, then H2D packed || D2H raw), same pinned buffers, "
+                             "all ranks concurrently, max over ranks",
         "steps": steps,
         "sample": "%d of the %d segments per GPU (%.0f MiB raw), pinned host buffers, wall clock around the "
                   "synchronous C-ABI calls" % (n_seg, args.segments, raw / 2**20),
     }
 
 
-def run_cpu_leg(args, gpu_payload=None, gpu_fields=0):
-    """The reference's CPU code timed on a bounded sample of the same workload.
-    gpu_payload(i) -> bytes of field i as the GPU arm encoded it: the sample is
-    the slab's first segments, so the two must be byte-identical (SURVEY 8d:
-    parity check in the same run)."""
+def run_cpu_leg(args, d_in, fields, gpu_payload=None, gpu_fields=0):
+    """The reference's CPU code timed on a bounded sample of the same workload: the
+    slab's first segments, the device generator's floats copied to the host.
+    gpu_payload(i) -> bytes of field i as the GPU arm encoded it; the two must be
+    byte-identical (parity check in the same run)."""
     threads = os.cpu_count() or 1
     n_seg = args.cpu_segments or max(1, min(threads, 32))
+    n_seg = min(n_seg, args.segments)
     threads = min(threads, n_seg)
-    orc, kind, gen, raw, payloads, one_step = cpu_baseline(threads, n_seg, SEG, 1024)
+    orc, kind = load_oracle()
+    fl = d_in[:n_seg * 6 * SEG].cpu().numpy().reshape(n_seg, 2, 3 * SEG)
+    pos = np.ascontiguousarray(fl[:, 0, :]).reshape(-1)
+    vel = np.ascontiguousarray(fl[:, 1, :]).reshape(-1)
+    del fl
+    raw, payloads, one_step = cpu_baseline(orc, pos, vel, threads, n_seg, SEG, seeds=[f[5] for f in fields])
     parity = None
-    if gpu_payload is not None and gen == "device generator":
+    if gpu_payload is not None:
         k = min(len(payloads), gpu_fields)
         same = sum(1 for i in range(k) if np.array_equal(gpu_payload(i), payloads[i]))
-        parity = {"fields_compared": k, "byte_identical": same, "ok": same == k}
+        parity = {"fields_compared": k, "byte_identical": same, "ok": same == k, "against": kind}
     one_step()
     te = td = 0.0
     reps = 0
@@ -557,13 +606,175 @@ def run_cpu_leg(args, gpu_payload=None, gpu_fields=0):
         te += a
         td += b
         reps += 1
-    return {
+    out = {
         "value": 2 * raw * reps / (te + td) / 1e9, "unit": UNIT, "cores": threads, "kind": kind,
         "encode_gbs": raw * reps / te / 1e9, "decode_gbs": raw * reps / td / 1e9,
-        "sample": "%d segments x 2^%d particles pos+vel (%.0f MiB raw) x %d passes, threads over fields, %s"
-                  % (n_seg, SEG_LOG2, raw / 2**20, reps, gen),
+        "sample": "%d segments x 2^%d particles pos+vel (%.0f MiB raw) x %d passes, threads over fields, "
+                  "device generator's floats" % (n_seg, SEG_LOG2, raw / 2**20, reps),
         "parity": parity,
     }
+    out.update(extra_cpu_figures(orc, one_step, SEG))
+    return out
+
+
+def sharded_parity(torch, dist, d_in, d_out, d_off, fields, dev, pick=(0, 1)):
+    """N > 1: every rank byte-compares some of its fields (floats of the 2048^3 box,
+    copied to the host) with the CPU oracle; the verdict is all-reduced."""
+    orc, kind = load_oracle()
+    offs = d_off.cpu().numpy()
+    same = 0
+    for i in pick:
+        off, n, code, delta, width, seed = fields[i]
+        host = d_in[off:off + 3 * n].cpu().numpy()
+        want = orc.encode_field(code, host, delta, width, seed=seed)
+        got = d_out[int(offs[i]):int(offs[i + 1])].cpu().numpy()
+        same += int(np.array_equal(got, want))
+    t = torch.tensor([same, len(pick)], dtype=torch.int64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    same, total = [int(v) for v in t.cpu()]
+    return {"fields_compared": total, "byte_identical": same, "ok": same == total, "against": kind,
+            "note": "fields %s of every rank's slab" % (list(pick),)}
+
+
+def read_headers(torch, d_out, d_off, nf):
+    """The fields' 64-byte headers as a structured array (one gather on the device)."""
+    offs = d_off[:nf].to(torch.int64)
+    idx = offs[:, None] + torch.arange(64, device=d_out.device, dtype=torch.int64)[None, :]
+    raw = d_out[idx.reshape(-1)].cpu().numpy().tobytes()
+    hd = np.dtype([("Magic", "<u4"), ("Version", "<u4"), ("FieldCode", "<u4"), ("ParticleLen", "<i4"),
+                   ("Depth", "u1"), ("Pad", "u1", 3), ("Width", "<f4"), ("X0", "<f4", 3), ("X1", "<f4", 3),
+                   ("BlockLen", "<u4"), ("DitherRun", "<u2"), ("DitherLanes", "<u2"), ("DitherSeed", "<u8")])
+    return np.frombuffer(raw, hd)
+
+
+SWEEP_DEPTHS = (6, 8, 10, 12, 14, 16, 18, 20, 22, 24)
+
+
+def run_sweep(torch, mc, codec, d_in, d_out, d_off, d_dec, fields, seg, peak, ngrid, first_id, n_seg):
+    """BASELINE configs[4]: the same 1024^3 slab at quantisation depths 6..24. For
+    every field Delta = maxDiff / 2^d * 1.0001, so that deltaToDepth
+    (/root/reference/src/quant.c:675-697) returns exactly d; encode
+    once, then time decode only (and the encoder at the same depth). Run on the
+    smooth field of the headline and on a rough one (white-noise displacement of
+    0.3 cells on top: deltas that do not shrink with the grid spacing)."""
+    nf = len(fields)
+    values = nf * 3 * seg
+    out = {"depths": list(SWEEP_DEPTHS), "delta_rule": "maxDiff/2^d*1.0001 per field", "reps": 3, "fields": {}}
+
+    def one_field(kind):
+        codec.encode_dev(d_in, mc.make_descs(fields), nf, d_out, d_off)
+        torch.cuda.synchronize()
+        if codec.status() != 0:
+            raise SystemExit("sweep: device-side error in the default encode")
+        hd = read_headers(torch, d_out, d_off, nf)
+        md = np.max(hd["X1"] - hd["X0"], axis=1).astype(np.float32)
+        rows = []
+        codec.enable_kernel_timing(True)
+        for d in SWEEP_DEPTHS:
+            deltas = (md / np.float32(2.0 ** d) * np.float32(1.0001)).astype(np.float32)
+            fl = [(f[0], f[1], f[2], float(deltas[i]), f[4], f[5]) for i, f in enumerate(fields)]
+            descs = mc.make_descs(fl)
+            enc, dec = [], []
+            for rep in range(4):  # first pass untimed
+                codec.encode_dev(d_in, descs, nf, d_out, d_off)
+                codec.decode_dev(d_out, d_off, descs, nf, d_dec)
+                torch.cuda.synchronize()
+                if rep:
+                    kt = codec.kernel_times()
+                    enc.append(kt["k_encode"])
+                    dec.append(kt["k_unpack_dequant"])
+            if codec.status() != 0:
+                raise SystemExit("sweep: device-side error at depth %d" % d)
+            hd2 = read_headers(torch, d_out, d_off, nf)
+            depth_ok = bool((hd2["Depth"] == d).all())
+            comp = int(d_off[nf].item())
+            c = comp / values
+            # error bound on two fields: |x - x'| <= Delta (mod L)
+            # (the bound is Delta plus the float spacing at the values themselves: at depth
+            # 24 a bin of a 100-wide box is narrower than one ulp of 100)
+            worst = 0.0
+            for i in (0, 1):
+                off, n, code, delta, width, _ = fl[i]
+                x = d_in[off:off + 3 * n].double()
+                err = (x - d_dec[off:off + 3 * n].double()).abs()
+                if width > 0:
+                    err = torch.minimum(err, width - err)
+                tol = delta + 2.0 * 2.0 ** -23 * max(float(x.abs().max()), width)
+                worst = max(worst, float(err.max()) / tol)
+            em, dm = float(np.mean(enc)), float(np.mean(dec))
+            alg = (4.0 + c) * values
+            rows.append({
+                "depth": d, "depth_ok": depth_ok, "compressed_bytes_per_value": round(c, 4),
+                "payload_bits_per_value": round(8.0 * (comp - nf * mc.field_fixed_bytes(seg)) / values, 3),
+                "decode_ms": round(dm, 4), "decode_raw_gbs": round(4.0 * values / (dm * 1e-3) / 1e9, 1),
+                "decode_achieved_gbs": round(alg / (dm * 1e-3) / 1e9, 1), "decode_frac": round(alg / (dm * 1e-3) / 1e9 / peak, 4),
+                "encode_ms": round(em, 4), "encode_achieved_gbs": round(alg / (em * 1e-3) / 1e9, 1),
+                "encode_frac": round(alg / (em * 1e-3) / 1e9 / peak, 4),
+                "roundtrip_max_err_over_tol": round(worst, 4),
+                "ok": bool(depth_ok and worst <= 1.0 + 1e-3),
+            })
+        codec.enable_kernel_timing(False)
+        out["fields"][kind] = rows
+
+    one_field("smooth")
+    generate(codec, d_in, ngrid, first_id, n_seg, seg, noise_cells=0.3)
+    torch.cuda.synchronize()
+    # the rough field at the headline's own accuracies (pos 1e-3, vel 1), then the sweep
+    descs = mc.make_descs(fields)
+    codec.enable_kernel_timing(True)
+    enc, dec = [], []
+    for rep in range(4):
+        codec.encode_dev(d_in, descs, nf, d_out, d_off)
+        codec.decode_dev(d_out, d_off, descs, nf, d_dec)
+        torch.cuda.synchronize()
+        if rep:
+            kt = codec.kernel_times()
+            enc.append(kt["k_encode"])
+            dec.append(kt["k_unpack_dequant"])
+    codec.enable_kernel_timing(False)
+    comp = int(d_off[nf].item())
+    c = comp / values
+    alg = (4.0 + c) * values
+    out["rough_default_accuracy"] = {
+        "noise_cells": 0.3, "compressed_bytes_per_value": round(c, 4),
+        "payload_bits_per_value": round(8.0 * (comp - nf * mc.field_fixed_bytes(seg)) / values, 3),
+        "encode_ms": round(float(np.mean(enc)), 4), "encode_frac": round(alg / (np.mean(enc) * 1e-3) / 1e9 / peak, 4),
+        "decode_ms": round(float(np.mean(dec)), 4), "decode_frac": round(alg / (np.mean(dec) * 1e-3) / 1e9 / peak, 4),
+    }
+    one_field("rough")
+    out["ok"] = all(r["ok"] for rows in out["fields"].values() for r in rows)
+    generate(codec, d_in, ngrid, first_id, n_seg, seg)  # back to the headline's field
+    torch.cuda.synchronize()
+    return out
+
+
+def host_ceiling(torch, h_in, h_out_bytes, dev, raw, comp, steps=3):
+    """What pinned host memory and PCIe allow for the e2e copy pattern with no
+    kernels at all: (H2D raw || D2H compressed) then (H2D compressed || D2H raw),
+    plain cudaMemcpyAsync on two streams."""
+    d_raw = torch.empty(raw, dtype=torch.uint8, device=dev)
+    d_comp = torch.empty(comp, dtype=torch.uint8, device=dev)
+    h_raw = h_in.view(torch.uint8)[:raw]
+    h_comp = h_out_bytes[:comp]
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def phase(a_dst, a_src, b_dst, b_src):
+        with torch.cuda.stream(s1):
+            a_dst.copy_(a_src, non_blocking=True)
+        with torch.cuda.stream(s2):
+            b_dst.copy_(b_src, non_blocking=True)
+        s1.synchronize()
+        s2.synchronize()
+
+    phase(d_raw, h_raw, h_comp, d_comp)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        phase(d_raw, h_raw, h_comp, d_comp)   # encode's copies
+        phase(d_comp, h_comp, h_raw, d_raw)   # decode's copies
+    el = time.perf_counter() - t0
+    del d_raw, d_comp
+    return el / steps
 
 
 def load_traffic(kernel):
@@ -589,6 +800,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer e2e leg (kernel experiments)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-gather", action="store_true", help="N>1: skip the (separately reported) stream gather")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the depth sweep (BASELINE configs[4])")
+    ap.add_argument("--same-seed", action="store_true",
+                    help="one dither seed for all fields (one shared stream table) instead of one per field")
     args = ap.parse_args()
     if args.steps < 1:
         args.steps = 1

@@ -153,6 +153,13 @@ void mnwcuda_SetDitherSeed(void *buffer, uint64_t seed);
 int mnwcuda_GenerateZeldovich(MnwCudaCtx *ctx, int32_t ngrid, float boxWidth,
                               uint64_t seed, int64_t firstId, int64_t count,
                               float *d_pos, float *d_vel, void *stream);
+/* The same with a white-noise displacement of +-noiseCells grid cells per
+ * component on top (a hash of the particle id): a rough field whose deltas do
+ * not shrink with the grid spacing, for the wide-block paths. */
+int mnwcuda_GenerateZeldovichRough(MnwCudaCtx *ctx, int32_t ngrid, float boxWidth,
+                                   uint64_t seed, int64_t firstId, int64_t count,
+                                   float noiseCells, float *d_pos, float *d_vel,
+                                   void *stream);
 
 #ifdef __cplusplus
 }

@@ -17,7 +17,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "libminnow_cuda.so")
+# (MNWCUDA_LIB: kernel experiments load a differently built library of the same ABI)
+LIB_PATH = os.environ.get("MNWCUDA_LIB") or os.path.join(_HERE, "libminnow_cuda.so")
 HOST_LIB_PATH = os.path.join(_HERE, "libminnow_host.so")
 
 FIELD_POSN = 0x506F736E
@@ -119,6 +120,8 @@ EXPORTS = {
     "mnwcuda_SetDitherSeed": (None, [C.c_void_p, C.c_uint64]),
     "mnwcuda_GenerateZeldovich": (C.c_int, [C.c_void_p, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64,
                                             C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mnwcuda_GenerateZeldovichRough": (C.c_int, [C.c_void_p, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64,
+                                                 C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 class _Seq(C.Structure):
@@ -290,11 +293,11 @@ class Codec:
     def status(self, stream=None):
         return lib().mnwcuda_Status(self.ctx, _stream_ptr(stream))
 
-    def generate(self, ngrid, box, seed, first_id, count, d_pos=None, d_vel=None, stream=None):
-        rc = lib().mnwcuda_GenerateZeldovich(self.ctx, ngrid, box, seed, first_id, count,
-                                             d_pos.data_ptr() if d_pos is not None else None,
-                                             d_vel.data_ptr() if d_vel is not None else None,
-                                             _stream_ptr(stream))
+    def generate(self, ngrid, box, seed, first_id, count, d_pos=None, d_vel=None, stream=None, noise_cells=0.0):
+        rc = lib().mnwcuda_GenerateZeldovichRough(self.ctx, ngrid, box, seed, first_id, count, noise_cells,
+                                                  d_pos.data_ptr() if d_pos is not None else None,
+                                                  d_vel.data_ptr() if d_vel is not None else None,
+                                                  _stream_ptr(stream))
         if rc:
             raise ValueError("mnwcuda_GenerateZeldovich: %d" % rc)
 

@@ -20,7 +20,7 @@ __device__ __forceinline__ void pack_lane(const uint32_t (&r)[kChunk], uint32_t 
 #pragma unroll
     for (int i = 0; i < kChunk; i++) {
         const int off = (i * W) & 31;
-        acc |= r[i] << off;
+        acc += r[i] << off;  // disjoint bits: the sum is the OR, and shift-and-add is one instruction
         if (off + W >= 32) {
             st[skew(base + ((i * W) >> 5))] = acc;
             acc = (off + W > 32) ? (r[i] >> ((32 - off) & 31)) : 0u;

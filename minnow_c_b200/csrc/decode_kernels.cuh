@@ -34,10 +34,29 @@ constexpr int kJumpPows = 26;
 // seed, consistency checks; decides whose stream table to use (fields with the
 // seed of field 0 share table 0).
 // ---------------------------------------------------------------------------
+// A region is usable only if it is 16-byte aligned, its offsets are ordered and it
+// holds at least the header and the block table: checked before the first load, so
+// that a truncated or corrupt stream raises kErrPayload instead of faulting.
+__device__ __forceinline__ bool region_ok(const DecodeParams &p, int f) {
+    const uint64_t a = p.offsets[f], b = p.offsets[f + 1];
+    return (a & 15u) == 0 && b >= a && b - a >= (uint64_t)(64 + 48 * (int64_t)p.fields[f].nb);
+}
+
 __global__ void k_parse_headers(DecodeParams p) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= p.nFields) return;
     const DevField fd = p.fields[f];
+    DevQuant q;
+    if (!region_ok(p, f)) {
+        atomicCAS(p.error, 0, kErrPayload);
+        for (int c = 0; c < 3; c++) q.X0[c] = q.X1[c] = 0.0f;
+        q.maxDiff = q.width = 0.0f;
+        q.depth = 0xffffffffu;
+        p.quant[f] = q;
+        p.seeds[f] = 0;
+        p.tableOf[f] = f;
+        return;
+    }
     const uint8_t *src = p.in + p.offsets[f];
     __align__(16) MnwDiffHeader h;
     for (int i = 0; i < 4; i++)
@@ -46,7 +65,6 @@ __global__ void k_parse_headers(DecodeParams p) {
               h.DitherRun == MNWCUDA_DITHER_RUN && h.DitherLanes == MNWCUDA_DITHER_LANES &&
               h.Depth <= 24 && h.FieldCode == fd.fieldCode;
     if (!ok) atomicCAS(p.error, 0, kErrPayload);
-    DevQuant q;
     float md = 0.0f;
     for (int c = 0; c < 3; c++) {
         q.X0[c] = h.X0[c];
@@ -59,10 +77,15 @@ __global__ void k_parse_headers(DecodeParams p) {
     q.width = h.Width;
     p.quant[f] = q;
     p.seeds[f] = h.DitherSeed;
-    const MnwDiffHeader *h0 = reinterpret_cast<const MnwDiffHeader *>(p.in + p.offsets[0]);
-    int64_t mine = (3 * (int64_t)fd.nb + kRun - 1) / kRun * 32;
-    int64_t zero = (3 * (int64_t)p.fields[0].nb + kRun - 1) / kRun * 32;
-    p.tableOf[f] = (h.DitherSeed == h0->DitherSeed && mine <= zero) ? 0 : f;
+    // fields with the seed of field 0 (and no more streams than it) share its table
+    bool share = false;
+    if (f > 0 && region_ok(p, 0)) {
+        const MnwDiffHeader *h0 = reinterpret_cast<const MnwDiffHeader *>(p.in + p.offsets[0]);
+        int64_t mine = (3 * (int64_t)fd.nb + kRun - 1) / kRun * 32;
+        int64_t zero = (3 * (int64_t)p.fields[0].nb + kRun - 1) / kRun * 32;
+        share = h.DitherSeed == h0->DitherSeed && mine <= zero;
+    }
+    p.tableOf[f] = share ? 0 : f;
 }
 
 // splitmix64, src/rand.c:114-121
@@ -109,6 +132,60 @@ __global__ void __launch_bounds__(128) k_stream_states(DecodeParams p) {
     uint64_t *dst = p.states + ((int64_t)f * p.maxStreams + k) * 2;
     dst[0] = s0;
     dst[1] = s1;
+}
+
+// ---------------------------------------------------------------------------
+// K3a for batches of many fields with their own seeds. J^k does not depend on the
+// seed: k_jump_table tabulates the columns of J^k for every stream index once per
+// context (2 KiB per k), and k_stream_states_tab applies J^k to the seed states of
+// all fields that own a table -- one CTA per k with the matrix in shared memory,
+// threads over fields, one 128x128 GF(2) matrix-vector product per stream (about
+// 900 instructions) instead of one per set bit of k per field.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void gf2_matvec(const ulonglong2 *col, uint64_t &s0, uint64_t &s1) {
+    uint64_t a = 0, b = 0;
+#pragma unroll 8
+    for (int i = 0; i < 64; i++) {
+        const ulonglong2 c0 = col[i], c1 = col[64 + i];
+        const uint64_t m0 = 0ull - ((s0 >> i) & 1ull);
+        const uint64_t m1 = 0ull - ((s1 >> i) & 1ull);
+        a ^= (c0.x & m0) ^ (c1.x & m1);
+        b ^= (c0.y & m0) ^ (c1.y & m1);
+    }
+    s0 = a;
+    s1 = b;
+}
+
+// one thread per (k, column i): column i of J^k = product over the set bits of k of J^(2^bit) applied to e_i
+__global__ void __launch_bounds__(128) k_jump_table(const uint64_t *jumpPow, ulonglong2 *tab, int64_t nStreams) {
+    const int64_t k = blockIdx.x;
+    const int i = threadIdx.x;
+    if (k >= nStreams) return;
+    uint64_t s0 = i < 64 ? 1ull << i : 0ull, s1 = i >= 64 ? 1ull << (i - 64) : 0ull;
+    for (int bit = 0; bit < kJumpPows; bit++) {
+        if (!((k >> bit) & 1)) continue;
+        gf2_matvec(reinterpret_cast<const ulonglong2 *>(jumpPow) + bit * 128, s0, s1);
+    }
+    tab[k * 128 + i] = make_ulonglong2(s0, s1);
+}
+
+__global__ void __launch_bounds__(128) k_stream_states_tab(DecodeParams p, const ulonglong2 *tab) {
+    __shared__ ulonglong2 col[128];
+    const int64_t k = blockIdx.x;
+    col[threadIdx.x] = tab[k * 128 + threadIdx.x];
+    __syncthreads();
+    for (int f = threadIdx.x; f < p.nFields; f += blockDim.x) {
+        if (p.tableOf[f] != f) continue;
+        const int64_t nStreams = (3 * (int64_t)p.fields[f].nb + kRun - 1) / kRun * 32;
+        if (k >= nStreams) continue;
+        uint64_t sm = p.seeds[f];
+        uint64_t s0 = splitmix_next(sm);
+        uint64_t s1 = splitmix_next(sm);
+        gf2_matvec(col, s0, s1);
+        uint64_t *dst = p.states + ((int64_t)f * p.maxStreams + k) * 2;
+        dst[0] = s0;
+        dst[1] = s1;
+    }
 }
 
 // ---------------------------------------------------------------------------

@@ -23,22 +23,32 @@
 namespace mnw {
 
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kEncWarps = 20;        // per CTA (one CTA per SM): producer, 18 consumers, a service warp (scan in CTA 0, reduce in CTA 1)
-constexpr int kEncConsumers = 18;
-constexpr int kEncStages = 44;       // input ring: 4 KiB blocks per SM (TMA, 128-byte swizzle)
+#ifndef MNW_ENC_CONSUMERS
+#define MNW_ENC_CONSUMERS 18
+#endif
+constexpr int kEncConsumers = MNW_ENC_CONSUMERS;
+constexpr int kEncWarps = kEncConsumers + 2;  // per CTA (one CTA per SM): producer, consumers, a service warp (scan in CTA 0, reduce in CTA 1)
 constexpr int kEncStageBytes = 4096;
 constexpr int kGroupSlots = 32;      // slots per ticket
 constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
+constexpr int kFifo = 8;             // parked blocks a consumer can remember
+constexpr int kArenaWords = 832;     // per consumer: packed blocks waiting for their offset, in shared memory
+                                     // (one block of the widest kind, 33 x 25 + 1 words, or four typical ones)
+// input ring: 4 KiB blocks (TMA, 128-byte swizzle), as many stages as the SM's shared memory holds
+// next to the consumers' arenas and records
+constexpr int kEncPerConsumer = kFifo * (16 + 8 + 8) + 64 + kArenaWords * 4;
+constexpr int kEncStages = (232448 - 32 - kEncConsumers * kEncPerConsumer) / (kEncStageBytes + 2 * 8 + 80 + 4);
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
-constexpr int kEncCtrlBytes = 2 * kEncStages * 8 + kEncStages * 80 + 16 + kEncStages * 4;
+constexpr int kEncCtrlBytes = (2 * kEncStages * 8 + kEncStages * 80 + 16 + kEncStages * 4 + 15) & ~15;
 constexpr int kEncFifoOff = kEncCtrlOff + kEncCtrlBytes;   // per consumer: records of its parked blocks
-constexpr int kEncFifoBytes = kEncConsumers * 8 * (16 + 8 + 8);
+constexpr int kEncFifoBytes = kEncConsumers * kFifo * (16 + 8 + 8);
 constexpr int kEncStatOff = kEncFifoOff + kEncFifoBytes;   // per consumer: 8 phase clocks (MNWCUDA_ENCODE_STATS)
-constexpr int kArenaWords = 512;     // per consumer: packed blocks waiting for their offset, in shared memory
 constexpr int kEncArenaOff = kEncStatOff + kEncConsumers * 64;
 constexpr int kEncSmemBytes = kEncArenaOff + kEncConsumers * kArenaWords * 4;
 static_assert(kEncSmemBytes <= 232448, "k_encode: more shared memory than an SM has");
+static_assert(kArenaWords >= 33 * 25 + 1, "k_encode: the arena must hold one block of any width");
+static_assert(kEncStages >= 16, "k_encode: too few ring stages");
 constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bits x 1024, 16-byte padded
 
 constexpr uint32_t kAggReady = 0x8000u;       // in a 16-bit size word

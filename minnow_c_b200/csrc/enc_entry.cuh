@@ -50,7 +50,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     ff.slots = p.scratch + ((size_t)blockIdx.x * kEncConsumers + c) * kFifo * kSlotWords;
     ff.arena = reinterpret_cast<uint32_t *>(encSmem + kEncArenaOff) + c * kArenaWords;
     ff.head = ff.count = 0;
-    ff.aTail = ff.aUsed = 0;
+    ff.aTail = ff.aUsed = ff.resident = 0;
     ff.wst = nullptr;
     if (kStats && p.stats) {
         ff.wst = reinterpret_cast<unsigned long long *>(encSmem + kEncStatOff) + c * 8;
@@ -66,9 +66,12 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         // (inline asm: the compiler otherwise wraps the one-lane atomicAdd in its
         // warp-aggregation sequence, a dozen instructions per claim)
         uint32_t seq = 0;
-        if (lane == 0)
-            asm volatile("atom.shared.add.u32 %0, [%1], 1;"
-                         : "=r"(seq) : "r"((uint32_t)__cvta_generic_to_shared(rc.qHead)) : "memory");
+        asm volatile("{\n\t"
+                     ".reg .pred one;\n\t"
+                     "elect.sync _|one, 0xffffffff;\n\t"
+                     "@one atom.shared.add.u32 %0, [%1], 1;\n\t"
+                     "}"
+                     : "+r"(seq) : "r"((uint32_t)__cvta_generic_to_shared(rc.qHead)) : "memory");
         seq = __shfl_sync(kFull, seq, 0);
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
@@ -97,8 +100,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             }
         } else if (d.kind == kWorkB) {
             if (!b_block<kFromQ, kStats>(p, d, stage, rc, s, ff, lane)) {
-                drain = true;
-                release_stage(rc, s, false, lane);
+                drain = true;  // (b_block hands its stage back before anything that can time out)
                 continue;
             }
             if (kStats) {

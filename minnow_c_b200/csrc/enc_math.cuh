@@ -64,23 +64,31 @@ __device__ __forceinline__ float unwrap_t(float v, const Unwrap &u) {
 // bit pattern is kQBias + q; the bias cancels in the deltas. The clamp t >= 1
 // becomes fmin against the largest index (an integer, so trunc commutes).
 // s >= 0 always: x0 is the minimum of the very same unwrapped values.
-template <bool kPos, bool kBiased>
-__device__ __forceinline__ void quantise32(const float *stage, int lane, const Unwrap &uw, float x0,
-                                           double scale, uint32_t top, uint32_t (&q)[kChunk]) {
-    const float topf = (float)top;
+// the lane's 32 consecutive values of a staged block (128-byte swizzle), as bit patterns
+__device__ __forceinline__ void load_block32(const float *stage, int lane, uint32_t (&q)[kChunk]) {
 #pragma unroll
     for (int j = 0; j < 8; j++) {
-        const float4 e4 = reinterpret_cast<const float4 *>(stage)[swz_chunk(lane, j)];
-        float e[4] = {e4.x, e4.y, e4.z, e4.w};
+        const uint4 e4 = reinterpret_cast<const uint4 *>(stage)[swz_chunk(lane, j)];
+        q[j * 4 + 0] = e4.x;
+        q[j * 4 + 1] = e4.y;
+        q[j * 4 + 2] = e4.z;
+        q[j * 4 + 3] = e4.w;
+    }
+}
+
+// in place: q holds the raw floats' bit patterns on entry, the indices on return
+template <bool kPos, bool kBiased>
+__device__ __forceinline__ void quantise32(const Unwrap &uw, float x0, double scale, uint32_t top,
+                                           uint32_t (&q)[kChunk]) {
+    const float topf = (float)top;
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            float u = e[i];
-            if (kPos) u = unwrap_t(u, uw);
-            const float a = __fsub_rn(u, x0);
-            const float s = __double2float_rn(__dmul_rn((double)a, scale));
-            if (kBiased) q[j * 4 + i] = __float_as_uint(__fadd_rz(fminf(s, topf), 8388608.0f));
-            else q[j * 4 + i] = min(__float2uint_rz(s), top);
-        }
+    for (int i = 0; i < kChunk; i++) {
+        float u = __uint_as_float(q[i]);
+        if (kPos) u = unwrap_t(u, uw);
+        const float a = __fsub_rn(u, x0);
+        const float s = __double2float_rn(__dmul_rn((double)a, scale));
+        if (kBiased) q[i] = __float_as_uint(__fadd_rz(fminf(s, topf), 8388608.0f));
+        else q[i] = min(__float2uint_rz(s), top);
     }
 }
 

@@ -70,6 +70,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
 // bounded wait: a barrier that never completes raises kErrTimeout instead of hanging
 // (false: the caller leaves the kernel, it must not touch the ring again)
 __device__ __forceinline__ bool mbar_wait(int *error, uint64_t *bar, uint32_t parity, int site) {
+    if (mbar_try_wait(bar, parity)) return true;  // the usual case: no counters, no clock
     uint32_t spins = 0;
     unsigned long long t0 = 0;
     while (!mbar_try_wait(bar, parity)) {
@@ -181,6 +182,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                 pc.tHi = pc.tLo = pc.x0 = 0.0f;
                 pc.scale = 0.0;
                 pc.depth = 0;
+                if (kFromQ) pc.depth = __ldg(&p.quant[d.f].depth);  // given by the caller: the range check needs it
                 if (!kFromQ && fdp->fieldCode == field_Posn) {
                     const Unwrap uw = make_unwrap(__ldg(p.in + fdp->ioOff + (int64_t)d.comp * n), fdp->width);
                     pc.tHi = uw.tHi;

@@ -22,7 +22,19 @@ struct GenParams {
     float velPerLen;  // velocity = velPerLen * displacement
     int64_t firstId, count;
     float *pos, *vel;  // planar [3][count], may be null
+    float noise;       // white-noise displacement per component, uniform in [-noise, noise) box units (0: none)
+    uint64_t noiseSeed;
 };
+
+// splitmix64 finaliser as a hash of (seed, particle id, component): the noise of a
+// particle does not depend on how the ids are cut into calls
+__device__ __forceinline__ float gen_noise(uint64_t seed, int64_t id, int c) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (uint64_t)(3 * id + c + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (float)(z >> 40) * (1.0f / 8388608.0f) - 1.0f;  // [-1, 1)
+}
 
 __constant__ GenModes cModes;
 
@@ -47,6 +59,10 @@ __global__ void __launch_bounds__(256) k_zeldovich(GenParams p) {
     const float cell = p.L / (float)N;
     float psi[3] = {px, py, pz};
     int idx[3] = {ix, iy, iz};
+    if (p.noise > 0.0f) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) psi[c] += p.noise * gen_noise(p.noiseSeed, id, c);
+    }
 #pragma unroll
     for (int c = 0; c < 3; c++) {
         if (p.pos) {

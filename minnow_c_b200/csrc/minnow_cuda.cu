@@ -69,6 +69,9 @@ struct MnwCudaCtx {
     uint64_t ditherSeed = 0;
     Scratch fields, quant, minmax, tileState, seeds, tableOf, states, misc, ring;
     Scratch ioA, ioB, ioC;  // host-buffer entry points: device staging
+    Scratch jumpTab;        // columns of J^k for k < tabStreams (k_jump_table), built on first use
+    int64_t tabStreams = 0;
+    cudaEvent_t tabEv = nullptr;
     uint64_t *jumpPow = nullptr;
     int *error = nullptr;     // device flag
     uint32_t *ticket = nullptr;
@@ -198,6 +201,7 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
     for (cudaEvent_t &e : ctx->pipeEv) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CUDA_CHECK(cudaEventCreateWithFlags(&ctx->tabEv, cudaEventDisableTiming));
     return ctx;
 }
 
@@ -206,7 +210,8 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->seeds,
-                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC};
+                      &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC,
+                      &ctx->jumpTab};
     for (Scratch *s : all) s->release();
     cudaFree(ctx->jumpPow);
     cudaFree(ctx->error);
@@ -217,6 +222,7 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->pipeEv)
         if (e) cudaEventDestroy(e);
+    if (ctx->tabEv) cudaEventDestroy(ctx->tabEv);
     if (ctx->encStats) {
         unsigned long long h[16];
         cudaMemcpy(h, ctx->encStats, sizeof(h), cudaMemcpyDeviceToHost);
@@ -309,6 +315,9 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
 // ---------------------------------------------------------------------------
 namespace {
 
+constexpr int64_t kTabMinFields = 16;       // below: k_stream_states (one product per set bit of k per field)
+constexpr int64_t kTabMaxStreams = 1 << 16;  // above: the table would exceed 128 MiB
+
 struct Plan {
     std::vector<DevField> fields;
     int64_t nTiles = 0, nBlocks = 0, nTasks = 0, fixedTotal = 0, maxStreams = 0;
@@ -323,7 +332,7 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
     bool uniform = true;
     for (int64_t i = 0; i < nFields; i++) {
         const MnwFieldDesc &d = h[i];
-        if (d.ParticleLen < 0) return -1;
+        if (d.ParticleLen < 0 || d.Offset < 0) return -1;
         if (d.FieldCode != field_Posn && d.FieldCode != field_Velc) return -3;
         DevField &f = pl.fields[(size_t)i];
         f.ioOff = d.Offset;
@@ -531,8 +540,23 @@ extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, con
     ctx->launches++;
     mark(ctx, 6, s);
     if (pl.nTasks > 0) {
-        dim3 grid((unsigned)((pl.maxStreams + 127) / 128), (unsigned)nFields);
-        k_stream_states<<<grid, 128, 0, s>>>(p);
+        // Many fields: one matrix-vector product per stream against the tabulated J^k
+        // (built once per context); few fields: the jump-matrix powers directly.
+        if (nFields >= kTabMinFields && pl.maxStreams <= kTabMaxStreams) {
+            if (ctx->tabStreams < pl.maxStreams) {
+                CUDA_CHECK(cudaStreamSynchronize(s));  // the old table may still be read
+                ulonglong2 *tab = static_cast<ulonglong2 *>(ctx->jumpTab.need((size_t)pl.maxStreams * 2048));
+                k_jump_table<<<(unsigned)pl.maxStreams, 128, 0, s>>>(ctx->jumpPow, tab, pl.maxStreams);
+                CUDA_CHECK(cudaEventRecord(ctx->tabEv, s));
+                ctx->tabStreams = pl.maxStreams;
+                ctx->launches++;
+            }
+            CUDA_CHECK(cudaStreamWaitEvent(s, ctx->tabEv, 0));
+            k_stream_states_tab<<<(unsigned)pl.maxStreams, 128, 0, s>>>(p, static_cast<const ulonglong2 *>(ctx->jumpTab.ptr));
+        } else {
+            dim3 grid((unsigned)((pl.maxStreams + 127) / 128), (unsigned)nFields);
+            k_stream_states<<<grid, 128, 0, s>>>(p);
+        }
         mark(ctx, 7, s);
         const unsigned dgrid = (unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps);
         k_unpack_dequant<false><<<dgrid, kDecWarps * 32, 0, s>>>(p, pl.nTasks);
@@ -632,7 +656,8 @@ extern "C" Field mnwcuda_DecodeField(CField cf, void *buffer) {
     MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
     if (!ctx) MNW_PANIC("mnwcuda_DecodeField needs the buffer returned by MnwCudaDAlloc_v0_9.");
     CUDA_CHECK(cudaSetDevice(ctx->device));
-    if (cf.DataLen < (int64_t)sizeof(MnwDiffHeader)) MNW_PANIC("mnwcuda_DecodeField: payload too short.");
+    if (cf.Hd.ParticleLen < 0 || cf.DataLen < mnwcuda_FieldFixedBytes(cf.Hd.ParticleLen))
+        MNW_PANIC("mnwcuda_DecodeField: payload too short.");
     MnwDiffHeader h;
     memcpy(&h, cf.Data, sizeof(h));
     MnwFieldDesc d;
@@ -914,7 +939,8 @@ extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
 extern "C" QField MnwCudaDecompress_v0_9(CField cf, void *buffer) {
     MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
     if (!ctx) MNW_PANIC("MnwCudaDecompress_v0_9 needs the buffer returned by MnwCudaDAlloc_v0_9.");
-    if (cf.DataLen < (int64_t)sizeof(MnwDiffHeader)) MNW_PANIC("MnwCudaDecompress_v0_9: payload too short.");
+    if (cf.Hd.ParticleLen < 0 || cf.DataLen < mnwcuda_FieldFixedBytes(cf.Hd.ParticleLen))
+        MNW_PANIC("MnwCudaDecompress_v0_9: payload too short.");
     CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->own;
     MnwDiffHeader h;
@@ -992,7 +1018,13 @@ static inline uint64_t host_splitmix(uint64_t &s) {
 extern "C" int mnwcuda_GenerateZeldovich(MnwCudaCtx *ctx, int32_t ngrid, float boxWidth, uint64_t seed,
                                          int64_t firstId, int64_t count, float *d_pos, float *d_vel,
                                          void *stream) {
-    if (!ctx || ngrid <= 0 || count < 0) return -1;
+    return mnwcuda_GenerateZeldovichRough(ctx, ngrid, boxWidth, seed, firstId, count, 0.0f, d_pos, d_vel, stream);
+}
+
+extern "C" int mnwcuda_GenerateZeldovichRough(MnwCudaCtx *ctx, int32_t ngrid, float boxWidth, uint64_t seed,
+                                              int64_t firstId, int64_t count, float noiseCells, float *d_pos,
+                                              float *d_vel, void *stream) {
+    if (!ctx || ngrid <= 0 || count < 0 || !(noiseCells >= 0.0f)) return -1;
     if (count == 0) return 0;
     CUDA_CHECK(cudaSetDevice(ctx->device));
     // 64 integer wave-vectors with |k_i| <= 8, amplitude ~ |k|^-2 along k,
@@ -1030,6 +1062,8 @@ extern "C" int mnwcuda_GenerateZeldovich(MnwCudaCtx *ctx, int32_t ngrid, float b
     p.count = count;
     p.pos = d_pos;
     p.vel = d_vel;
+    p.noise = (float)(noiseCells * cell);
+    p.noiseSeed = seed ^ 0x6d6e77526f756768ull;
     k_zeldovich<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(p);
     ctx->launches++;
     CUDA_CHECK(cudaGetLastError());

@@ -10,6 +10,7 @@
 #define _POSIX_C_SOURCE 200809L
 #include "minnow_oracle.h"
 
+#include <math.h>
 #include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
@@ -18,6 +19,13 @@
 /* ------------------------------------------------------------------ */
 /* primitives                                                          */
 /* ------------------------------------------------------------------ */
+
+static uint64_t splitmix64(uint64_t *s) { /* src/rand.c:114-121 */
+    uint64_t z = (*s += 0x9E3779B97F4A7C15ULL);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
 
 #ifdef ORC_USE_REFERENCE
 
@@ -41,7 +49,11 @@ uint64_t ref_rand_u64(uint64_t state[2]);
 float ref_rand_float(uint64_t state[2]);
 void ref_rand_jump(uint64_t state[2]);
 
+#ifdef ORC_REFERENCE_DEBUG
+const char *orc_flavour(void) { return "reference-debug"; }
+#else
 const char *orc_flavour(void) { return "reference"; }
+#endif
 
 void orc_undo_periodic(float *x, int64_t n, float L) { ref_undo_periodic(x, n, L); }
 void orc_periodic(float *x, int64_t n, float L) { ref_periodic(x, n, L); }
@@ -168,12 +180,6 @@ void orc_rand_jump(uint64_t state[2]) {
     state[1] = b;
 }
 
-static uint64_t splitmix64(uint64_t *s) { /* src/rand.c:114-121 */
-    uint64_t z = (*s += 0x9E3779B97F4A7C15ULL);
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-    return z ^ (z >> 31);
-}
 
 /* src/rand.c:22-39: stream i is stream i-1 jumped by 2^64 draws. */
 void orc_rand_seed(uint64_t seed, int64_t n, uint64_t *states) {
@@ -581,4 +587,105 @@ double orc_bench_decode(const uint8_t *const *payloads, const int64_t *lens,
     p.decode = 1; p.payloads = payloads; p.lens = lens; p.n = n;
     p.nFields = nFields;
     return run_jobs(&p, threads, NULL);
+}
+
+/* ------------------------------------------------------------------ */
+/* bench input on the host: the same synthetic snapshot the device       */
+/* generator makes (64 sine modes drawn by splitmix64, amplitude          */
+/* ~ |k|^-2 along k, rms displacement 1.5 cells, v = 200 psi / cell,      */
+/* optional white noise), so that the --impl reference arm of bench.py    */
+/* never has to load the CUDA library. Same formulas, host libm: the      */
+/* floats agree with the device's to rounding, not bit for bit (nothing   */
+/* compares them). Nothing in the reference corresponds to this.          */
+/* ------------------------------------------------------------------ */
+#define ORC_GEN_MODES 64
+
+typedef struct GenJob {
+    int tid, threads, ngrid;
+    float L, velPerLen, noise;
+    uint64_t noiseSeed;
+    int64_t firstId, count;
+    const int *kx, *ky, *kz;
+    const float *phase, *ax, *ay, *az;
+    float *pos, *vel;
+} GenJob;
+
+static float gen_noise(uint64_t seed, int64_t id, int c) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ULL * (uint64_t)(3 * id + c + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    return (float)(z >> 40) * (1.0f / 8388608.0f) - 1.0f;
+}
+
+static void *gen_worker(void *arg) {
+    GenJob *j = arg;
+    const int N = j->ngrid;
+    const float piOverN = 3.14159265358979f / (float)N;
+    const float cell = j->L / (float)N;
+    int64_t lo = j->count * j->tid / j->threads, hi = j->count * (j->tid + 1) / j->threads;
+    for (int64_t i = lo; i < hi; i++) {
+        int64_t id = j->firstId + i;
+        int idx[3] = {(int)(id % N), (int)((id / N) % N), (int)(id / ((int64_t)N * N))};
+        float psi[3] = {0, 0, 0};
+        for (int m = 0; m < ORC_GEN_MODES; m++) {
+            int t = j->kx[m] * (2 * idx[0] + 1) + j->ky[m] * (2 * idx[1] + 1) + j->kz[m] * (2 * idx[2] + 1);
+            t %= 2 * N;
+            float sn = sinf((float)t * piOverN + j->phase[m]);
+            psi[0] = fmaf(j->ax[m], sn, psi[0]);
+            psi[1] = fmaf(j->ay[m], sn, psi[1]);
+            psi[2] = fmaf(j->az[m], sn, psi[2]);
+        }
+        for (int c = 0; c < 3; c++) {
+            if (j->noise > 0) psi[c] += j->noise * gen_noise(j->noiseSeed, id, c);
+            if (j->pos) {
+                float x = ((float)idx[c] + 0.5f) * cell + psi[c];
+                x -= j->L * floorf(x / j->L);
+                if (!(x >= 0.0f && x < j->L)) x = 0.0f;
+                j->pos[(int64_t)c * j->count + i] = x;
+            }
+            if (j->vel) j->vel[(int64_t)c * j->count + i] = j->velPerLen * psi[c];
+        }
+    }
+    return NULL;
+}
+
+int orc_gen_zeldovich(int32_t ngrid, float L, uint64_t seed, int64_t firstId,
+                      int64_t count, float noiseCells, float *pos, float *vel,
+                      int threads) {
+    if (ngrid <= 0 || count < 0) return -1;
+    int kx[ORC_GEN_MODES], ky[ORC_GEN_MODES], kz[ORC_GEN_MODES];
+    float phase[ORC_GEN_MODES], fx[ORC_GEN_MODES], fy[ORC_GEN_MODES], fz[ORC_GEN_MODES];
+    double ax[ORC_GEN_MODES], ay[ORC_GEN_MODES], az[ORC_GEN_MODES], sumsq = 0.0;
+    uint64_t s = seed;
+    for (int i = 0; i < ORC_GEN_MODES; i++) {
+        do {
+            kx[i] = (int)(splitmix64(&s) % 17) - 8;
+            ky[i] = (int)(splitmix64(&s) % 17) - 8;
+            kz[i] = (int)(splitmix64(&s) % 17) - 8;
+        } while (kx[i] == 0 && ky[i] == 0 && kz[i] == 0);
+        double k2 = (double)kx[i] * kx[i] + (double)ky[i] * ky[i] + (double)kz[i] * kz[i];
+        double a = 1.0 / k2, inv = 1.0 / sqrt(k2);
+        phase[i] = (float)((double)(splitmix64(&s) >> 11) * (1.0 / 9007199254740992.0) * 6.283185307179586);
+        ax[i] = a * kx[i] * inv; ay[i] = a * ky[i] * inv; az[i] = a * kz[i] * inv;
+        sumsq += a * a;
+    }
+    const double cell = (double)L / ngrid;
+    const double scale = 1.5 * cell / sqrt(sumsq / 2.0);
+    for (int i = 0; i < ORC_GEN_MODES; i++) {
+        fx[i] = (float)(ax[i] * scale); fy[i] = (float)(ay[i] * scale); fz[i] = (float)(az[i] * scale);
+    }
+    if (threads < 1) threads = 1;
+    pthread_t *th = malloc((size_t)threads * sizeof(*th));
+    GenJob *jobs = malloc((size_t)threads * sizeof(*jobs));
+    for (int t = 0; t < threads; t++) {
+        GenJob g = {t, threads, ngrid, L, (float)(200.0 / cell), (float)(noiseCells * cell),
+                    seed ^ 0x6d6e77526f756768ULL, firstId, count, kx, ky, kz, phase, fx, fy, fz, pos, vel};
+        jobs[t] = g;
+        pthread_create(&th[t], NULL, gen_worker, &jobs[t]);
+    }
+    for (int t = 0; t < threads; t++) pthread_join(th[t], NULL);
+    free(th);
+    free(jobs);
+    return 0;
 }

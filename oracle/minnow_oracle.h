@@ -113,7 +113,14 @@ double orc_bench_encode(uint32_t fieldCode, const float *data, int32_t n,
 double orc_bench_decode(const uint8_t *const *payloads, const int64_t *lens,
                         int32_t n, int64_t nFields, int threads);
 
-const char *orc_flavour(void); /* "port" or "reference" */
+/* bench input made on the host (same recipe as the device generator; not
+ * bit-identical to it): ids [firstId, firstId+count) of an ngrid^3 box, planar
+ * float32; pos / vel may be NULL */
+int orc_gen_zeldovich(int32_t ngrid, float L, uint64_t seed, int64_t firstId,
+                      int64_t count, float noiseCells, float *pos, float *vel,
+                      int threads);
+
+const char *orc_flavour(void); /* "port", "reference" or "reference-debug" */
 
 #ifdef __cplusplus
 }

@@ -76,6 +76,8 @@ def _bind(lib):
                                            C.c_float, C.c_int, C.POINTER(C.c_int64)]),
         "orc_bench_decode": (C.c_double, [C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int32,
                                            C.c_int64, C.c_int]),
+        "orc_gen_zeldovich": (C.c_int, [C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64, C.c_float,
+                                        C.c_void_p, C.c_void_p, C.c_int]),
         "orc_flavour": (C.c_char_p, []),
     }
     for name, (res, args) in sig.items():
@@ -205,6 +207,16 @@ class Oracle:
             raise ValueError("oracle decode_q failed: %d" % rc)
         return q[:3 * n]
 
+    def gen_zeldovich(self, ngrid, box, seed, first_id, count, noise_cells=0.0, threads=1):
+        """Host twin of the device generator's recipe (not bit-identical): (pos[3*count], vel[3*count])."""
+        pos = np.empty(3 * count, np.float32)
+        vel = np.empty(3 * count, np.float32)
+        rc = self.lib.orc_gen_zeldovich(ngrid, box, seed, first_id, count, noise_cells,
+                                        pos.ctypes.data, vel.ctypes.data, threads)
+        if rc:
+            raise ValueError("orc_gen_zeldovich: %d" % rc)
+        return pos, vel
+
     def bench_encode(self, field_code, data, n, n_fields, delta, width, threads):
         data = np.ascontiguousarray(data, dtype=np.float32).reshape(-1)
         nbytes = C.c_int64()
@@ -246,6 +258,16 @@ def reference():
         path = os.path.join(ORACLE_DIR, "_ref", "liboracle_ref.so")
         _cache["ref"] = Oracle(path) if os.path.exists(path) else None
     return _cache["ref"]
+
+
+def reference_debug():
+    """The reference composition with the reference compiled -D DEBUG (its own
+    Makefile's flags), or None. CPU-baseline figure only."""
+    if "refdbg" not in _cache:
+        build()
+        path = os.path.join(ORACLE_DIR, "_ref", "liboracle_ref_debug.so")
+        _cache["refdbg"] = Oracle(path) if os.path.exists(path) else None
+    return _cache["refdbg"]
 
 
 def flavours():

@@ -21,6 +21,14 @@ def codec():
 
 
 orc = _oracle.port()
+# every oracle flavour present: the restated port and, where oracle/_ref was built
+# (it travels to the GPU box), the same composition on the reference's own objects
+FLAVOURS = _oracle.flavours()
+
+
+@pytest.fixture(params=FLAVOURS, ids=[o.flavour for o in FLAVOURS])
+def checker(request):
+    return request.param
 
 
 def cases():
@@ -64,22 +72,22 @@ CASES = list(cases())
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
-def test_encode_field_bytes_match_oracle(codec, case):
+def test_encode_field_bytes_match_oracle(codec, case, checker):
     _, code, data, delta, width = case
     codec.set_dither_seed(77)
     got = codec.encode_field(code, data, delta, width)
-    want = orc.encode_field(code, data, delta, width, seed=77)
+    want = checker.encode_field(code, data, delta, width, seed=77)
     assert got.size == want.size
     assert np.array_equal(got[:64], want[:64]), "field header differs"
     assert np.array_equal(got, want)
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
-def test_decode_field_floats_match_oracle(codec, case):
+def test_decode_field_floats_match_oracle(codec, case, checker):
     _, code, data, delta, width = case
     n = data.size // 3
-    payload = orc.encode_field(code, data, delta, width, seed=123456789)
-    want = orc.decode_field(payload)
+    payload = checker.encode_field(code, data, delta, width, seed=123456789)
+    want = checker.decode_field(payload)
     got, rep_delta = codec.decode_field(code, n, payload)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
     hd = _oracle.parse_header(payload)
@@ -230,7 +238,12 @@ def test_generator_roundtrip_accuracy(codec):
     assert payload.size < 0.6 * hp.nbytes
 
 
-def test_bench_sized_slab_matches_oracle(codec):
+def test_bench_sized_slab_matches_oracle(codec, checker):
+    orc = checker  # noqa: F841 (shadows the module-level port on purpose)
+    _bench_sized_slab(codec, checker)
+
+
+def _bench_sized_slab(codec, orc):
     """Eight segments of 2^22 particles, positions and velocities (the bench's
     field size: 4096 blocks per component, every fast path of the persistent
     encoder) in one batch: every field's bytes against the oracle, twice (the
@@ -272,7 +285,8 @@ def test_bench_sized_slab_matches_oracle(codec):
 
 
 @pytest.mark.parametrize("depth", list(range(0, 25)))
-def test_depth_sweep_matches_oracle(codec, depth):
+def test_depth_sweep_matches_oracle(codec, depth, checker):
+    orc = checker
     """BASELINE config 4: the same data at every quantisation depth 0..24 (Delta
     chosen so that deltaToDepth, src/quant.c:684-688, lands on `depth`), encode
     bytes and decoded floats against the oracle. Depth 24 takes the encoder's
