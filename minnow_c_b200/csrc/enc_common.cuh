@@ -158,9 +158,26 @@ __device__ __forceinline__ void st_stream_u4(uint4 *p, uint4 v) {
                  : "memory");
 }
 
-// every spin-wait gives up after a fraction of a second and raises kErrTimeout
-// instead of hanging the device: error[1] = site, error[2..3] = block
-constexpr uint32_t kSpinLimit = 1u << 19;
+// every wait on another warp's work gives up after kWaitLimitNs of wall clock
+// (%globaltimer, looked at every 256 polls) and raises kErrTimeout instead of
+// hanging the device: error[1] = site, error[2..3] = block. The limit is far above
+// anything a healthy launch waits for (a whole 24 GiB batch encodes in 10 ms), also
+// under a profiler's serialised replay.
+constexpr unsigned long long kWaitLimitNs = 4000000000ull;
+struct SpinClock {
+    uint32_t spins = 0;
+    unsigned long long t0 = 0;
+};
+__device__ __forceinline__ bool spin_expired(SpinClock &c) {
+    if ((++c.spins & 255u) != 0) return false;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (c.t0 == 0) {
+        c.t0 = t;
+        return false;
+    }
+    return t - c.t0 > kWaitLimitNs;
+}
 __device__ __noinline__ void spin_timeout(int *error, int site, int64_t blk) {
     if (atomicCAS(error, 0, kErrTimeout) == 0) {
         error[1] = site;

@@ -19,10 +19,10 @@ __device__ __forceinline__ void release_stage(const RingCtrl &rc, int s, bool wr
 __device__ __forceinline__ bool wait_quant(const EncodeParams &p, WorkDesc &d) {
     const uint64_t *w = p.fq + ((int64_t)d.f * 3 + d.comp) * 2;
     uint64_t w0 = ld_relaxed_u64(w), w1 = ld_relaxed_u64(w + 1);
-    uint32_t spins = 0;
+    SpinClock clk;
     while (!(w0 & w1 & kFqValid)) {
         __nanosleep(100);
-        if (++spins > kSpinLimit) { spin_timeout(p.error, 1, d.blk); return false; }
+        if (spin_expired(clk)) { spin_timeout(p.error, 1, d.blk); return false; }
         w0 = ld_relaxed_u64(w);
         w1 = ld_relaxed_u64(w + 1);
     }
@@ -146,10 +146,10 @@ __device__ __forceinline__ uint64_t peek_prefix(const EncodeParams &p, int64_t b
 __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff, int lane) {
     const int64_t pl = ff.blk[ff.head];
     uint64_t pre = 0;
-    uint32_t spins = 0;
+    SpinClock clk;
     while (!block_prefix(p.blkRel, p.winBase, pl, pre)) {
         __nanosleep(200);
-        if (++spins > kSpinLimit) { spin_timeout(p.error, 2, pl); return false; }
+        if (spin_expired(clk)) { spin_timeout(p.error, 2, pl); return false; }
     }
     place_finish(p, ff, pre, lane);
     return true;

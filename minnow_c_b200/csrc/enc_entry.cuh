@@ -75,8 +75,8 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         seq = __shfl_sync(kFull, seq, 0);
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
-        for (uint32_t spins = 0; rc.uses[s] < use;) {
-            if (++spins > (kSpinLimit << 6)) { spin_timeout(p.error, 7, -1); return; }
+        for (SpinClock clk; rc.uses[s] < use;) {
+            if (spin_expired(clk)) { spin_timeout(p.error, 7, -1); return; }
         }
         if (!mbar_wait(p.error, rc.full + s, use & 1u, 5)) return;
         WorkDesc d = rc.desc[s];

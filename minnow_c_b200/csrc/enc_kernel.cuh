@@ -116,17 +116,17 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
                     if (base + j * 256 + lane * 8 + i >= p.nBlocks) wds[i >> 1] = (wds[i >> 1] & ~(0xffffu << (16 * (i & 1)))) | (kAggReady << (16 * (i & 1)));
             }
         }
-        uint32_t spins = 0;
+        SpinClock clk;
         while (true) {
             bool all = true;
 #pragma unroll
             for (int j = 0; j < 4; j++) all = all && agg_ready(cur[j]);
             if (__all_sync(kFull, all)) break;
-            if (++spins > kSpinLimit) {
+            if (spin_expired(clk)) {
                 if (lane == 0) spin_timeout(p.error, 3, base);
                 return;
             }
-            if (spins > 16) __nanosleep(100);
+            if (clk.spins > 16) __nanosleep(100);
 #pragma unroll
             for (int j = 0; j < 4; j++)
                 if (!agg_ready(cur[j])) {
@@ -231,7 +231,7 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
         if (more) red_load(p, base + kRedWin, lane, nxt);
         const int64_t winEnd = min(base + kRedWin, p.nBlocks);
         const bool whole = base + kRedWin <= p.nBlocks;
-        uint32_t spins = 0;
+        SpinClock clk;
         while (true) {
             bool all = true;
             if (whole) {
@@ -246,11 +246,11 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
                 }
             }
             if (__all_sync(kFull, all)) break;
-            if (++spins > kSpinLimit) {
+            if (spin_expired(clk)) {
                 if (lane == 0) spin_timeout(p.error, 6, base);
                 return;
             }
-            if (spins > 16) __nanosleep(100);
+            if (clk.spins > 16) __nanosleep(100);
 #pragma unroll
             for (int j = 0; j < 8; j++)
                 if (!mm_ready(cur[j])) cur[j] = ld_relaxed_u4(p.blkMM + base + j * 64 + lane * 2);

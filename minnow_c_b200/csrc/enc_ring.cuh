@@ -78,7 +78,7 @@ __device__ __forceinline__ bool mbar_wait(int *error, uint64_t *bar, uint32_t pa
             unsigned long long t;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
             if (t0 == 0) t0 = t;
-            else if (t - t0 > 1000000000ull) { spin_timeout(error, site, -1); return false; }
+            else if (t - t0 > kWaitLimitNs) { spin_timeout(error, site, -1); return false; }
         }
     }
     return true;
@@ -245,7 +245,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                 unsigned long long t;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
                 if (t0 == 0) t0 = t;
-                else if (t - t0 > 1000000000ull) {
+                else if (t - t0 > kWaitLimitNs) {
                     if (!filled) spin_timeout(p.error, 4, -1);
                     return;
                 }

@@ -447,11 +447,20 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     if (const char *e = getenv("MNWCUDA_ENCODE_CTAS"))  // debugging: does the time scale with the SMs?
         if (atoi(e) >= 8 && atoi(e) < ctas) ctas = atoi(e);
     if (ctas < 2) ctas = 2;  // the reduce warp lives in CTA 1
+    // The CTAs of k_encode wait for each other's results (scan warp in CTA 0, reduce
+    // warp in CTA 1, ticket order), so all of them must be resident at once: a
+    // cooperative launch starts the grid only when every CTA has an SM, whatever else
+    // the device is running; the grid is sized by the occupancy query, never above it.
+    const void *fn = fromQ ? (const void *)k_encode<true, false>
+                           : q.stats ? (const void *)k_encode<false, true> : (const void *)k_encode<false, false>;
+    int perSm = 0;
+    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, kEncWarps * 32, kEncSmemBytes));
+    if (perSm < 1) MNW_PANIC("k_encode does not fit an SM of this device.");
+    if (ctas > (int64_t)perSm * ctx->smCount) ctas = (int64_t)perSm * ctx->smCount;
     ctx->lastEnc = q;
     ctx->haveLastEnc = true;
-    if (fromQ) k_encode<true, false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
-    else if (q.stats) k_encode<false, true><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
-    else k_encode<false, false><<<(unsigned)ctas, kEncWarps * 32, kEncSmemBytes, s>>>(q, map);
+    void *args[2] = {&q, &map};
+    CUDA_CHECK(cudaLaunchCooperativeKernel(fn, dim3((unsigned)ctas), dim3(kEncWarps * 32), args, kEncSmemBytes, s));
     ctx->launches++;
     CUDA_CHECK(cudaGetLastError());
 }

@@ -189,3 +189,75 @@ def test_rough_generator_is_deterministic_and_wider(codec):
     smooth = codec.encode_field(mc.FIELD_POSN, hc, 1e-3, 100.0)
     assert np.array_equal(rough, orc.encode_field(mc.FIELD_POSN, ha, 1e-3, 100.0, seed=1))
     assert rough.size > smooth.size
+
+
+def _small_batch(codec_, seed0):
+    d_in, fields = _slab(codec_, 4, 1 << 18, 256, seed0)
+    return d_in, fields
+
+
+def test_encode_while_other_kernels_hold_sms(codec):
+    """k_encode's CTAs wait for each other, so the launch is cooperative: with
+    long-running kernels of other streams sitting on SMs it starts when the whole
+    grid fits, and ends with the right bytes -- never with a timeout (status 5)."""
+    d_in, fields = _small_batch(codec, 100)
+    want, offs_want = _encode(codec, d_in, fields)
+    streams = [torch.cuda.Stream() for _ in range(12)]
+    for st in streams:  # ~50 ms of spinning single-CTA kernels, one per stream
+        with torch.cuda.stream(st):
+            torch.cuda._sleep(100_000_000)
+    enc_stream = torch.cuda.Stream()
+    nf = len(fields)
+    d_out = torch.zeros(sum(mc.field_bound(f[1]) for f in fields), dtype=torch.uint8, device="cuda")
+    d_off = torch.zeros(nf + 1, dtype=torch.int64, device="cuda")
+    with torch.cuda.stream(enc_stream):
+        codec.encode_dev(d_in, mc.make_descs(fields), nf, d_out, d_off, stream=enc_stream.cuda_stream)
+        assert codec.status(enc_stream.cuda_stream) == 0
+    torch.cuda.synchronize()
+    offs = d_off.cpu().numpy()
+    assert np.array_equal(offs, offs_want)
+    assert np.array_equal(d_out[:int(offs[nf])].cpu().numpy(), want)
+
+
+def test_two_contexts_encode_concurrently():
+    """The reference makes one Compressor per field (src/funcs.c:145-158): two
+    contexts, two host threads, each encoding its own batch on its own stream at the
+    same time. Both finish with status 0 and the bytes of a solo run."""
+    import threading
+    ca, cb = mc.Codec(0), mc.Codec(0)
+    try:
+        jobs = []
+        for c, seed0 in ((ca, 300), (cb, 400)):
+            d_in, fields = _small_batch(c, seed0)
+            want, offs = _encode(c, d_in, fields)
+            jobs.append((c, d_in, fields, want, offs))
+        results = [None, None]
+
+        def run(i):
+            c, d_in, fields, _, _ = jobs[i]
+            torch.cuda.set_device(0)
+            st = torch.cuda.Stream()
+            nf = len(fields)
+            d_out = torch.zeros(sum(mc.field_bound(f[1]) for f in fields), dtype=torch.uint8, device="cuda")
+            d_off = torch.zeros(nf + 1, dtype=torch.int64, device="cuda")
+            torch.cuda.synchronize()
+            ok = True
+            for _ in range(20):
+                c.encode_dev(d_in, mc.make_descs(fields), nf, d_out, d_off, stream=st.cuda_stream)
+                ok = ok and c.status(st.cuda_stream) == 0
+            offs = d_off.cpu().numpy()
+            results[i] = (ok, offs, d_out[:int(offs[nf])].cpu().numpy())
+
+        th = [threading.Thread(target=run, args=(i,)) for i in range(2)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        for i in range(2):
+            ok, offs, got = results[i]
+            assert ok
+            assert np.array_equal(offs, jobs[i][4])
+            assert np.array_equal(got, jobs[i][3])
+    finally:
+        ca.close()
+        cb.close()
