@@ -436,13 +436,17 @@ static int decode_blocks(const uint8_t *in, int64_t len, uint32_t *q) {
         int64_t cnt = n - b * ORC_BLOCK_LEN;
         if (cnt > ORC_BLOCK_LEN) cnt = ORC_BLOCK_LEN;
         OrcBlockEntry e = table[g];
+        uint32_t *qb = q + (size_t)c * n + (size_t)b * ORC_BLOCK_LEN;
+        if (e.Width == ORC_WIDTH_DAMAGED) { /* orc_seg_from_bytes: the block's checksum failed */
+            for (int64_t j = 0; j < cnt; j++) qb[j] = 0; /* placeholders: the values come out as NaN */
+            continue;
+        }
         if (e.Width > 32) return -3;
         int64_t nw = orc_pack_words(cnt, (uint8_t)e.Width);
         int64_t start = fixed + (int64_t)e.Offset16 * 16;
         if (start + nw * 4 > len) return -1;
         memcpy(words, in + start, (size_t)nw * 4);
         orc_undo_uniform_pack(words, (uint8_t)e.Width, cnt, r);
-        uint32_t *qb = q + (size_t)c * n + (size_t)b * ORC_BLOCK_LEN;
         qb[0] = e.First;
         for (int64_t j = 1; j < cnt; j++)
             qb[j] = qb[j - 1] + r[j] + (uint32_t)e.MinDelta;
@@ -462,26 +466,20 @@ int orc_diff_decode_q(const uint8_t *in, int64_t len, uint64_t *q) {
     return rc;
 }
 
-/* DFunc + quant_Field as intended (src/quant.c:451-551 with the fixes listed
- * in DESIGN.md): dx = maxDiff for every component, util.c:237-238's two-step
- * dither, explicit seed, one stream per (task, lane), 32 values per visit. */
-int orc_diff_decode_field(const uint8_t *in, int64_t len, float *out,
-                          uint32_t *q_out) {
-    if (len < (int64_t)sizeof(OrcFieldHeader)) return -1;
-    OrcFieldHeader hd;
-    memcpy(&hd, in, sizeof(hd));
-    int32_t n = hd.ParticleLen;
+/* quant_Field as intended (src/quant.c:451-551 with the fixes listed in
+ * DESIGN.md): dx = maxDiff for every component, util.c:237-238's two-step
+ * dither, explicit seed, one stream per (task, lane), 32 values per visit.
+ * `damaged` (may be NULL): per block, non-zero = its values come out as NaN
+ * (the stream still advances, so the other blocks are unaffected). */
+static int dequantize(const OrcFieldHeader *hd, const uint32_t *q,
+                      const uint8_t *damaged, float *out) {
+    int32_t n = hd->ParticleLen;
     if (n <= 0) return n == 0 ? 0 : -1;
-    uint32_t *q = q_out;
-    if (!q) q = malloc((size_t)n * 3 * sizeof(uint32_t));
-    int rc = decode_blocks(in, len, q);
-    if (rc != 0) { if (!q_out) free(q); return rc; }
-
     int64_t nb = orc_diff_nblocks(n);
     int64_t ns = orc_diff_nstreams(n);
     uint64_t *states = malloc((size_t)ns * 2 * sizeof(uint64_t));
-    orc_rand_seed(hd.DitherSeed, ns, states);
-    float md = max_diff(hd.X0, hd.X1);
+    orc_rand_seed(hd->DitherSeed, ns, states);
+    float md = max_diff(hd->X0, hd->X1);
 
     for (int64_t g = 0; g < 3 * nb; g++) {
         int64_t b = g % nb, c = g / nb;
@@ -493,17 +491,415 @@ int orc_diff_decode_field(const uint8_t *in, int64_t len, float *out,
             int64_t lo = lane * ORC_CHUNK;
             int64_t m = cnt - lo < ORC_CHUNK ? cnt - lo : ORC_CHUNK;
             orc_undo_uniform_bin_index(
-                q + base + lo, m, hd.Depth, hd.X0[c], md,
+                q + base + lo, m, hd->Depth, hd->X0[c], md,
                 states + 2 * (task * ORC_DITHER_LANES + lane),
                 out + base + lo);
         }
     }
-    if (hd.FieldCode == ORC_FIELD_POSN)
+    if (hd->FieldCode == ORC_FIELD_POSN)
         for (int c = 0; c < 3; c++)
-            orc_periodic(out + (size_t)c * n, n, hd.Width);
+            orc_periodic(out + (size_t)c * n, n, hd->Width);
+    if (damaged)
+        for (int64_t g = 0; g < 3 * nb; g++) {
+            if (!damaged[g]) continue;
+            int64_t b = g % nb, c = g / nb;
+            int64_t cnt = n - b * ORC_BLOCK_LEN;
+            if (cnt > ORC_BLOCK_LEN) cnt = ORC_BLOCK_LEN;
+            uint32_t nanBits = 0x7fc00000u;
+            for (int64_t j = 0; j < cnt; j++)
+                memcpy(out + (size_t)c * n + (size_t)b * ORC_BLOCK_LEN + j, &nanBits, 4);
+        }
     free(states);
-    if (!q_out) free(q);
     return 0;
+}
+
+/* the quantised values of a field (3n, as the literal QField boundary carries
+ * them) -> floats: the fixed quant_Field for Posn / Velc */
+int orc_dequantize_field(const OrcFieldHeader *hd, const uint64_t *q, float *out) {
+    int64_t m = 3 * (int64_t)hd->ParticleLen;
+    uint32_t *q32 = malloc((size_t)(m > 0 ? m : 1) * sizeof(uint32_t));
+    for (int64_t i = 0; i < m; i++) q32[i] = (uint32_t)q[i];
+    int rc = dequantize(hd, q32, NULL, out);
+    free(q32);
+    return rc;
+}
+
+/* DFunc + quant_Field */
+int orc_diff_decode_field(const uint8_t *in, int64_t len, float *out,
+                          uint32_t *q_out) {
+    if (len < (int64_t)sizeof(OrcFieldHeader)) return -1;
+    OrcFieldHeader hd;
+    memcpy(&hd, in, sizeof(hd));
+    int32_t n = hd.ParticleLen;
+    if (n <= 0) return n == 0 ? 0 : -1;
+    uint32_t *q = q_out;
+    if (!q) q = malloc((size_t)n * 3 * sizeof(uint32_t));
+    int rc = decode_blocks(in, len, q);
+    if (rc != 0) { if (!q_out) free(q); return rc; }
+    int64_t nb = orc_diff_nblocks(n);
+    uint8_t *damaged = calloc((size_t)(3 * nb), 1);
+    const OrcBlockEntry *table = (const OrcBlockEntry *)(in + sizeof(hd));
+    int any = 0;
+    for (int64_t g = 0; g < 3 * nb; g++)
+        if (table[g].Width == ORC_WIDTH_DAMAGED) { damaged[g] = 1; any = 1; }
+    rc = dequantize(&hd, q, any ? damaged : NULL, out);
+    free(damaged);
+    if (!q_out) free(q);
+    return rc;
+}
+
+/* ------------------------------------------------------------------ */
+/* integer fields: particle IDs and unsigned ints (lossless)            */
+/* ------------------------------------------------------------------ */
+
+#ifdef ORC_USE_REFERENCE
+int ref_quant_id(const uint64_t *ids, int32_t n, uint64_t width,
+                 uint64_t X0[3], uint64_t X1[3], uint64_t *q);
+int ref_undo_id(const uint64_t *q, int32_t n, uint64_t width,
+                const uint64_t X0[3], uint64_t *ids);
+int ref_quant_uint(const uint64_t *data, int32_t n, uint64_t *x0, uint64_t *x1,
+                   uint64_t *q);
+int ref_undo_uint(const uint64_t *q, int32_t n, uint64_t x0, uint64_t *out);
+
+int orc_id_quantize(const uint64_t *ids, int32_t n, uint64_t width,
+                    uint64_t X0[3], uint64_t X1[3], uint64_t *q) {
+    return ref_quant_id(ids, n, width, X0, X1, q);
+}
+int orc_id_dequantize(const uint64_t *q, int32_t n, uint64_t width,
+                      const uint64_t X0[3], uint64_t *ids) {
+    return ref_undo_id(q, n, width, X0, ids);
+}
+int orc_uint_quantize(const uint64_t *data, int32_t n, uint64_t *x0,
+                      uint64_t *x1, uint64_t *q) {
+    return ref_quant_uint(data, n, x0, x1, q);
+}
+int orc_uint_dequantize(const uint64_t *q, int32_t n, uint64_t x0, uint64_t *out) {
+    return ref_undo_uint(q, n, x0, out);
+}
+#else
+/* id() of src/quant.c:291-327: the id is split into three grid coordinates
+ * (x fastest), each component is unwrapped around its first element with
+ * util_U64UndoPeriodic (src/util.c:115-143: signed tests against +-L/2 from
+ * the second element on, then everything shifted up by L if the minimum went
+ * negative), and the component's minimum is subtracted. */
+int orc_id_quantize(const uint64_t *ids, int32_t n, uint64_t width,
+                    uint64_t X0[3], uint64_t X1[3], uint64_t *q) {
+    if (n <= 0 || width == 0) return -1;
+    for (int32_t i = 0; i < n; i++) {
+        q[i] = ids[i] % width;
+        q[(size_t)n + i] = (ids[i] / width) % width;
+        q[2 * (size_t)n + i] = ids[i] / (width * width);
+    }
+    const int64_t L = (int64_t)width;
+    for (int c = 0; c < 3; c++) {
+        int64_t *x = (int64_t *)(q + (size_t)c * n);
+        const int64_t x0 = x[0];
+        for (int32_t i = 1; i < n; i++) {
+            if (x[i] - x0 >= L / 2) x[i] -= L;
+            else if (x[i] - x0 < -L / 2) x[i] += L;
+        }
+        int64_t mn = x0;
+        for (int32_t i = 1; i < n; i++) if (x[i] < mn) mn = x[i];
+        if (mn < 0) for (int32_t i = 0; i < n; i++) x[i] += L;
+        /* util_U64MinMax, src/util.c:48-68 */
+        uint64_t *u = (uint64_t *)x, lo = u[0], hi = u[0];
+        for (int32_t i = 1; i < n; i++) {
+            if (u[i] > hi) hi = u[i];
+            if (u[i] < lo) lo = u[i];
+        }
+        X0[c] = lo;
+        X1[c] = hi;
+        for (int32_t i = 0; i < n; i++) u[i] -= lo;
+    }
+    return 0;
+}
+
+/* undoID, src/quant.c:553-587 */
+int orc_id_dequantize(const uint64_t *q, int32_t n, uint64_t width,
+                      const uint64_t X0[3], uint64_t *ids) {
+    if (n <= 0) return -1;
+    for (int32_t i = 0; i < n; i++) {
+        uint64_t x = q[i] + X0[0];
+        if (x >= width) x -= width;
+        uint64_t y = q[(size_t)n + i] + X0[1];
+        if (y >= width) y -= width;
+        uint64_t z = q[2 * (size_t)n + i] + X0[2];
+        if (z >= width) z -= width;
+        ids[i] = x + width * y + width * width * z;
+    }
+    return 0;
+}
+
+/* uint() / undoUint(), src/quant.c:373-398, 589-608 */
+int orc_uint_quantize(const uint64_t *data, int32_t n, uint64_t *x0,
+                      uint64_t *x1, uint64_t *q) {
+    if (n <= 0) return -1;
+    uint64_t lo = data[0], hi = data[0];
+    for (int32_t i = 1; i < n; i++) {
+        if (data[i] > hi) hi = data[i];
+        if (data[i] < lo) lo = data[i];
+    }
+    for (int32_t i = 0; i < n; i++) q[i] = data[i] - lo;
+    *x0 = lo;
+    *x1 = hi;
+    return 0;
+}
+int orc_uint_dequantize(const uint64_t *q, int32_t n, uint64_t x0, uint64_t *out) {
+    if (n <= 0) return -1;
+    for (int32_t i = 0; i < n; i++) out[i] = q[i] + x0;
+    return 0;
+}
+#endif
+
+static void put_u32(float *slot, uint32_t v) { memcpy(slot, &v, 4); }
+static uint32_t get_u32(const float *slot) { uint32_t v; memcpy(&v, slot, 4); return v; }
+
+/* Particle IDs as a Diff v0.9 payload: id() then the same delta + pack as the
+ * float fields. The header's Width / X0 / X1 slots hold the IDQuantization
+ * (src/types.h:97-99) as uint32 bit patterns; Depth = bit length of the widest
+ * component's range (at most 24, else -1). */
+int64_t orc_diff_encode_id_field(const uint64_t *ids, int32_t n, uint64_t width,
+                                 uint8_t *out, int64_t cap) {
+    OrcFieldHeader hd;
+    memset(&hd, 0, sizeof(hd));
+    hd.Magic = ORC_ALGO_DIFF;
+    hd.Version = ORC_VERSION_0_9;
+    hd.FieldCode = ORC_FIELD_PTID;
+    hd.ParticleLen = n;
+    hd.BlockLen = ORC_BLOCK_LEN;
+    hd.DitherRun = ORC_DITHER_RUN;
+    hd.DitherLanes = ORC_DITHER_LANES;
+    if (width == 0 || width >= ((uint64_t)1 << 31)) return -3;
+    put_u32(&hd.Width, (uint32_t)width);
+    uint64_t *q = malloc((size_t)(n > 0 ? n : 1) * 3 * sizeof(uint64_t));
+    if (n > 0) {
+        uint64_t X0[3], X1[3], range = 0;
+        orc_id_quantize(ids, n, width, X0, X1, q);
+        for (int c = 0; c < 3; c++) {
+            if (X1[c] >= ((uint64_t)1 << 32)) { free(q); return -1; }
+            put_u32(&hd.X0[c], (uint32_t)X0[c]);
+            put_u32(&hd.X1[c], (uint32_t)X1[c]);
+            if (X1[c] - X0[c] > range) range = X1[c] - X0[c];
+        }
+        if (range >= ((uint64_t)1 << 24)) { free(q); return -1; }
+        hd.Depth = (uint8_t)bit_length((uint32_t)range);
+    }
+    int64_t bytes = orc_diff_encode_q(&hd, q, out, cap);
+    free(q);
+    return bytes;
+}
+
+int orc_diff_decode_id_field(const uint8_t *in, int64_t len, uint64_t *ids) {
+    if (len < (int64_t)sizeof(OrcFieldHeader)) return -1;
+    OrcFieldHeader hd;
+    memcpy(&hd, in, sizeof(hd));
+    if (hd.FieldCode != ORC_FIELD_PTID) return -3;
+    int32_t n = hd.ParticleLen;
+    if (n <= 0) return n == 0 ? 0 : -1;
+    uint64_t *q = malloc((size_t)n * 3 * sizeof(uint64_t));
+    int rc = orc_diff_decode_q(in, len, q);
+    if (rc == 0) {
+        uint64_t X0[3] = {get_u32(&hd.X0[0]), get_u32(&hd.X0[1]), get_u32(&hd.X0[2])};
+        rc = orc_id_dequantize(q, n, get_u32(&hd.Width), X0, ids);
+        /* a damaged block (orc_seg_from_bytes) loses its particles' ids */
+        const OrcBlockEntry *table = (const OrcBlockEntry *)(in + sizeof(hd));
+        int64_t nb = orc_diff_nblocks(n);
+        for (int64_t g = 0; g < 3 * nb; g++)
+            if (table[g].Width == ORC_WIDTH_DAMAGED) {
+                int64_t b = g % nb, cnt = n - b * ORC_BLOCK_LEN;
+                if (cnt > ORC_BLOCK_LEN) cnt = ORC_BLOCK_LEN;
+                for (int64_t j = 0; j < cnt; j++) ids[b * ORC_BLOCK_LEN + j] = UINT64_MAX;
+            }
+    }
+    free(q);
+    return rc;
+}
+
+/* Unsigned integers: uint() (subtract the minimum), then the N values are coded
+ * as three runs of ceil(N/3) (the last run padded with its last value) through
+ * the same delta + pack. The header's X0[0..1] / X1[0..1] slots hold the 64-bit
+ * minimum and maximum (IntQuantization, src/types.h:77-79); ParticleLen in the
+ * payload header is the run length, the true count travels in CField.Hd. */
+int64_t orc_diff_encode_uint_field(const uint64_t *data, int32_t n,
+                                   uint8_t *out, int64_t cap) {
+    OrcFieldHeader hd;
+    memset(&hd, 0, sizeof(hd));
+    hd.Magic = ORC_ALGO_DIFF;
+    hd.Version = ORC_VERSION_0_9;
+    hd.FieldCode = ORC_FIELD_UNSI;
+    int32_t run = (int32_t)(((int64_t)n + 2) / 3);
+    hd.ParticleLen = run;
+    hd.BlockLen = ORC_BLOCK_LEN;
+    hd.DitherRun = ORC_DITHER_RUN;
+    hd.DitherLanes = ORC_DITHER_LANES;
+    uint64_t *q = malloc((size_t)(run > 0 ? run : 1) * 3 * sizeof(uint64_t));
+    if (n > 0) {
+        uint64_t x0, x1;
+        orc_uint_quantize(data, n, &x0, &x1, q);
+        for (int64_t i = n; i < 3 * (int64_t)run; i++) q[i] = q[n - 1];
+        if (x1 - x0 >= ((uint64_t)1 << 24)) { free(q); return -1; }
+        put_u32(&hd.X0[0], (uint32_t)x0); put_u32(&hd.X0[1], (uint32_t)(x0 >> 32));
+        put_u32(&hd.X1[0], (uint32_t)x1); put_u32(&hd.X1[1], (uint32_t)(x1 >> 32));
+        hd.Depth = (uint8_t)bit_length((uint32_t)(x1 - x0));
+    }
+    int64_t bytes = orc_diff_encode_q(&hd, q, out, cap);
+    free(q);
+    return bytes;
+}
+
+int orc_diff_decode_uint_field(const uint8_t *in, int64_t len, int32_t n, uint64_t *out) {
+    if (len < (int64_t)sizeof(OrcFieldHeader)) return -1;
+    OrcFieldHeader hd;
+    memcpy(&hd, in, sizeof(hd));
+    if (hd.FieldCode != ORC_FIELD_UNSI) return -3;
+    int32_t run = hd.ParticleLen;
+    if (n < 0 || (int64_t)n > 3 * (int64_t)run || ((int64_t)n + 2) / 3 != run) return -1;
+    if (n == 0) return 0;
+    uint64_t *q = malloc((size_t)run * 3 * sizeof(uint64_t));
+    int rc = orc_diff_decode_q(in, len, q);
+    if (rc == 0) {
+        uint64_t x0 = (uint64_t)get_u32(&hd.X0[0]) | ((uint64_t)get_u32(&hd.X0[1]) << 32);
+        rc = orc_uint_dequantize(q, n, x0, out);
+        const OrcBlockEntry *table = (const OrcBlockEntry *)(in + sizeof(hd));
+        int64_t nb = orc_diff_nblocks(run);
+        for (int64_t g = 0; g < 3 * nb; g++)
+            if (table[g].Width == ORC_WIDTH_DAMAGED) {
+                int64_t b = g % nb, c = g / nb, cnt = run - b * ORC_BLOCK_LEN;
+                if (cnt > ORC_BLOCK_LEN) cnt = ORC_BLOCK_LEN;
+                for (int64_t j = 0; j < cnt; j++) {
+                    int64_t i = c * run + b * ORC_BLOCK_LEN + j;
+                    if (i < n) out[i] = UINT64_MAX;
+                }
+            }
+    }
+    free(q);
+    return rc;
+}
+
+/* ------------------------------------------------------------------ */
+/* segment image (doc/header_format/header_format.tex:129-204)          */
+/* ------------------------------------------------------------------ */
+
+/* blocks of one Diff v0.9 field: block 0 = header + block table, then one per
+ * packed block in table order; lengths are multiples of 16 (so of 8, tex:198-204) */
+static int64_t field_run_len(const OrcSegField *f) {
+    if (f->FieldCode == ORC_FIELD_UNSI) return ((int64_t)f->ParticleLen + 2) / 3;
+    return f->ParticleLen;
+}
+int64_t orc_seg_field_blocks(const OrcSegField *f) {
+    return 1 + 3 * orc_diff_nblocks((int32_t)field_run_len(f));
+}
+static int64_t block_len_of(const OrcSegField *f, int64_t k) {
+    int32_t run = (int32_t)field_run_len(f);
+    int64_t nb = orc_diff_nblocks(run);
+    if (k == 0) return orc_diff_fixed_bytes(run);
+    const OrcBlockEntry *table = (const OrcBlockEntry *)(f->Data + sizeof(OrcFieldHeader));
+    int64_t g = k - 1, b = g % nb;
+    int64_t cnt = run - b * ORC_BLOCK_LEN;
+    if (cnt > ORC_BLOCK_LEN) cnt = ORC_BLOCK_LEN;
+    return (orc_pack_words(cnt, (uint8_t)table[g].Width) * 4 + 15) / 16 * 16;
+}
+
+int64_t orc_seg_bytes_bound(const OrcSegField *fields, int32_t nFields) {
+    int64_t total = 16 + 16 * (int64_t)nFields;
+    for (int32_t i = 0; i < nFields; i++) total += 8 * orc_seg_field_blocks(&fields[i]) + fields[i].DataLen;
+    return total;
+}
+
+/* SegmentHeader | FieldHeader[F] | BlockHeader[B] | blocks. FieldHeader is the
+ * code's struct (src/types.h:103-108, 4th word ParticleLen: what src/funcs.c:85
+ * serialises), BlockHeader {int32 Length; uint32 Checksum} (tex:182-185); the
+ * checksum is util_Checksum (start value 1, as the code has it, not the 0xff of
+ * tex:381-389); SegmentHeader.Checksum covers the 12 + 16F + 8B bytes behind it
+ * (tex:150-158). */
+int64_t orc_seg_to_bytes(const OrcSegField *fields, int32_t nFields,
+                         int32_t particleNum, uint8_t *out, int64_t cap) {
+    int64_t nBlocks = 0;
+    for (int32_t i = 0; i < nFields; i++) nBlocks += orc_seg_field_blocks(&fields[i]);
+    if (nBlocks >= ((int64_t)1 << 31)) return -5;
+    int64_t hdrBytes = 16 + 16 * (int64_t)nFields + 8 * nBlocks;
+    if (orc_seg_bytes_bound(fields, nFields) > cap) return -2;
+    int32_t *sh = (int32_t *)out;
+    sh[1] = (int32_t)nBlocks;
+    sh[2] = nFields;
+    sh[3] = particleNum;
+    uint8_t *fh = out + 16, *bh = fh + 16 * (int64_t)nFields, *dst = out + hdrBytes;
+    for (int32_t i = 0; i < nFields; i++) {
+        const OrcSegField *f = &fields[i];
+        uint32_t w[4] = {f->FieldCode, f->AlgoCode, f->AlgoVersion, (uint32_t)f->ParticleLen};
+        memcpy(fh + 16 * (int64_t)i, w, 16);
+        int64_t nbk = orc_seg_field_blocks(f), off = 0;
+        for (int64_t k = 0; k < nbk; k++) {
+            int64_t len = block_len_of(f, k);
+            if (off + len > f->DataLen) return -1;
+            int32_t len32 = (int32_t)len;
+            uint32_t sum = orc_checksum(f->Data + off, len);
+            memcpy(bh, &len32, 4);
+            memcpy(bh + 4, &sum, 4);
+            bh += 8;
+            off += len;
+        }
+        if (off != f->DataLen) return -1;
+        memcpy(dst, f->Data, (size_t)f->DataLen);
+        dst += f->DataLen;
+    }
+    uint32_t top = orc_checksum(out + 4, hdrBytes - 4);
+    memcpy(out, &top, 4);
+    return dst - out;
+}
+
+/* Inverse. fields[i].Data points into `bytes` (which is modified: the table
+ * entry of a block whose checksum fails gets Width = ORC_WIDTH_DAMAGED, so that
+ * only that block's particles are lost, tex:188-196); valid[i] = 0 when the
+ * field's block 0 (header + table) is damaged. Returns the number of fields,
+ * <0 when the headers themselves are damaged or inconsistent. */
+int32_t orc_seg_from_bytes(uint8_t *bytes, int64_t len, OrcSegField *fields,
+                           int32_t maxFields, int32_t *valid, int32_t *particleNum) {
+    if (len < 16) return -1;
+    int32_t sh[4];
+    memcpy(sh, bytes, 16);
+    int64_t nBlocks = sh[1];
+    int32_t nFields = sh[2];
+    if (nFields < 0 || nBlocks < 0 || nFields > maxFields) return -1;
+    int64_t hdrBytes = 16 + 16 * (int64_t)nFields + 8 * nBlocks;
+    if (hdrBytes > len) return -1;
+    if (orc_checksum(bytes + 4, hdrBytes - 4) != (uint32_t)sh[0]) return -4;
+    if (particleNum) *particleNum = sh[3];
+    const uint8_t *fh = bytes + 16, *bh = fh + 16 * (int64_t)nFields;
+    uint8_t *src = bytes + hdrBytes;
+    int64_t seen = 0;
+    for (int32_t i = 0; i < nFields; i++) {
+        uint32_t w[4];
+        memcpy(w, fh + 16 * (int64_t)i, 16);
+        OrcSegField *f = &fields[i];
+        f->FieldCode = w[0]; f->AlgoCode = w[1]; f->AlgoVersion = w[2]; f->ParticleLen = (int32_t)w[3];
+        f->Data = src;
+        int64_t nbk = orc_seg_field_blocks(f), off = 0;
+        if (seen + nbk > nBlocks) return -1;
+        valid[i] = 1;
+        int32_t run = (int32_t)field_run_len(f);
+        for (int64_t k = 0; k < nbk; k++) {
+            int32_t len32;
+            uint32_t sum;
+            memcpy(&len32, bh, 4);
+            memcpy(&sum, bh + 4, 4);
+            bh += 8;
+            if (len32 < 0 || src + off + len32 > bytes + len) return -1;
+            if (k == 0 && len32 != orc_diff_fixed_bytes(run)) return -1;
+            if (orc_checksum(src + off, len32) != sum) {
+                if (k == 0) valid[i] = 0;
+                else if (valid[i]) {
+                    OrcBlockEntry *table = (OrcBlockEntry *)(src + sizeof(OrcFieldHeader));
+                    table[k - 1].Width = ORC_WIDTH_DAMAGED;
+                }
+            }
+            off += len32;
+        }
+        f->DataLen = off;
+        src += off;
+        seen += nbk;
+    }
+    return seen == nBlocks ? nFields : -1;
 }
 
 /* ------------------------------------------------------------------ */

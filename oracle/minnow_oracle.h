@@ -27,6 +27,8 @@ extern "C" {
 /* ---- field / algorithm codes (src/types.h:8-20) ---- */
 #define ORC_FIELD_POSN 0x506f736eu
 #define ORC_FIELD_VELC 0x56656c63u
+#define ORC_FIELD_PTID 0x50746964u
+#define ORC_FIELD_UNSI 0x556e7369u
 #define ORC_ALGO_DIFF  0x44696666u
 #define ORC_VERSION_0_9 0x00000900u /* src/semver.c:93-94 */
 
@@ -51,6 +53,8 @@ typedef struct OrcFieldHeader { /* 64 bytes, little-endian */
     uint16_t DitherLanes;
     uint64_t DitherSeed;
 } OrcFieldHeader;
+
+#define ORC_WIDTH_DAMAGED 0xffffffffu /* table entry of a block whose checksum failed */
 
 typedef struct OrcBlockEntry { /* 16 bytes */
     uint32_t First;    /* q[0] of the block */
@@ -95,6 +99,40 @@ int64_t orc_diff_encode_field(uint32_t fieldCode, const float *data, int32_t n,
 /* payload -> float field (3n planar). Returns 0, <0 on malformed input. */
 int orc_diff_decode_field(const uint8_t *in, int64_t len, float *out,
                           uint32_t *q_out);
+
+/* quantised values (3n, the QField boundary) -> floats: the fixed quant_Field */
+int orc_dequantize_field(const OrcFieldHeader *hd, const uint64_t *q, float *out);
+
+/* integer fields (src/quant.c:291-327, 373-398, 553-608): quantisers alone and
+ * as Diff v0.9 payloads. q holds 3n values for ids, n for unsigned ints. */
+int orc_id_quantize(const uint64_t *ids, int32_t n, uint64_t width,
+                    uint64_t X0[3], uint64_t X1[3], uint64_t *q);
+int orc_id_dequantize(const uint64_t *q, int32_t n, uint64_t width,
+                      const uint64_t X0[3], uint64_t *ids);
+int orc_uint_quantize(const uint64_t *data, int32_t n, uint64_t *x0,
+                      uint64_t *x1, uint64_t *q);
+int orc_uint_dequantize(const uint64_t *q, int32_t n, uint64_t x0, uint64_t *out);
+int64_t orc_diff_encode_id_field(const uint64_t *ids, int32_t n, uint64_t width,
+                                 uint8_t *out, int64_t cap);
+int orc_diff_decode_id_field(const uint8_t *in, int64_t len, uint64_t *ids);
+int64_t orc_diff_encode_uint_field(const uint64_t *data, int32_t n,
+                                   uint8_t *out, int64_t cap);
+int orc_diff_decode_uint_field(const uint8_t *in, int64_t len, int32_t n, uint64_t *out);
+
+/* segment image: SegmentHeader | FieldHeader[] | BlockHeader[] | blocks
+ * (doc/header_format/header_format.tex:129-204) */
+typedef struct OrcSegField {
+    uint32_t FieldCode, AlgoCode, AlgoVersion;
+    int32_t ParticleLen;
+    uint8_t *Data;   /* the field's Diff v0.9 payload (CField.Data) */
+    int64_t DataLen;
+} OrcSegField;
+int64_t orc_seg_field_blocks(const OrcSegField *f);
+int64_t orc_seg_bytes_bound(const OrcSegField *fields, int32_t nFields);
+int64_t orc_seg_to_bytes(const OrcSegField *fields, int32_t nFields,
+                         int32_t particleNum, uint8_t *out, int64_t cap);
+int32_t orc_seg_from_bytes(uint8_t *bytes, int64_t len, OrcSegField *fields,
+                           int32_t maxFields, int32_t *valid, int32_t *particleNum);
 
 /* literal plugin boundary: quantized ints in / out (CFunc / DFunc shape) */
 int64_t orc_diff_encode_q(const OrcFieldHeader *hd, const uint64_t *q,

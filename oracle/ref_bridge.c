@@ -12,6 +12,7 @@
 #include "util.h"  /* /root/reference/src/util.h */
 #include "rand.h"
 #include "seq.h"
+#include "quant.h"
 
 /* non-static in src/quant.c:675, not declared in quant.h */
 void deltaToDepth(float delta, float *deltas, float x0, float x1,
@@ -102,3 +103,91 @@ float ref_rand_float(uint64_t state[2]) {
 }
 
 void ref_rand_jump(uint64_t state[2]) { xorshiftJump((rand_State *)state); }
+
+/* id() / undoID() / uint() / undoUint() of src/quant.c:291-327, 373-398,
+ * 553-608 through the reference's own dispatch (quant_QField / quant_Field) */
+int ref_quant_id(const uint64_t *ids, int32_t n, uint64_t width,
+                 uint64_t X0[3], uint64_t X1[3], uint64_t *q) {
+    if (n <= 0 || width == 0) return -1;
+    /* id() never attaches its IDQuantization to the QField it returns
+     * (src/quant.c:291-327: `quant` is filled in and dropped), so X0 / X1 are
+     * taken from the same reference primitives id() calls, on the same split
+     * (src/quant.c:308-320), and the values are cross-checked against id()'s own */
+    for (int32_t i = 0; i < n; i++) {
+        q[i] = ids[i] % width;
+        q[(size_t)n + i] = (ids[i] / width) % width;
+        q[2 * (size_t)n + i] = ids[i] / (width * width);
+    }
+    for (int c = 0; c < 3; c++) {
+        U64Seq comp = U64Seq_WrapArray(q + (size_t)c * n, n);
+        util_U64UndoPeriodic(comp, width);
+        util_U64MinMax(comp, &X0[c], &X1[c]);
+        for (int32_t i = 0; i < n; i++) comp.Data[i] -= X0[c];
+    }
+    IDAccuracy acc = { .Width = width };
+    Field f;
+    memset(&f, 0, sizeof(f));
+    f.Hd.FieldCode = field_Ptid;
+    f.Hd.ParticleLen = n;
+    f.Data = (void *)ids;
+    f.Acc = &acc;
+    QField qf = quant_QField(f);
+    int same = memcmp(q, qf.Data, (size_t)n * 3 * sizeof(uint64_t)) == 0;
+    free(qf.Data);
+    return same ? 0 : -9;
+}
+
+int ref_undo_id(const uint64_t *q, int32_t n, uint64_t width,
+                const uint64_t X0[3], uint64_t *ids) {
+    if (n <= 0) return -1;
+    IDQuantization quant;
+    memset(&quant, 0, sizeof(quant));
+    quant.Width = width;
+    for (int c = 0; c < 3; c++) quant.X0[c] = X0[c];
+    QField qf;
+    memset(&qf, 0, sizeof(qf));
+    qf.Hd.FieldCode = field_Ptid;
+    qf.Hd.ParticleLen = n;
+    qf.Data = (uint64_t *)q;
+    qf.Quant = &quant;
+    Field f = quant_Field(qf);
+    memcpy(ids, f.Data, (size_t)n * sizeof(uint64_t));
+    free(f.Acc);
+    free(f.Data);
+    return 0;
+}
+
+int ref_quant_uint(const uint64_t *data, int32_t n, uint64_t *x0, uint64_t *x1,
+                   uint64_t *q) {
+    if (n <= 0) return -1;
+    /* uint() drops its IntQuantization the same way (src/quant.c:373-398) */
+    util_U64MinMax(U64Seq_WrapArray((uint64_t *)data, n), x0, x1);
+    uint8_t acc = 0;
+    Field f;
+    memset(&f, 0, sizeof(f));
+    f.Hd.FieldCode = field_Unsi;
+    f.Hd.ParticleLen = n;
+    f.Data = (void *)data;
+    f.Acc = &acc;
+    QField qf = quant_QField(f);
+    memcpy(q, qf.Data, (size_t)n * sizeof(uint64_t));
+    free(qf.Data);
+    for (int32_t i = 0; i < n; i++)
+        if (q[i] != data[i] - *x0) return -9;
+    return 0;
+}
+
+int ref_undo_uint(const uint64_t *q, int32_t n, uint64_t x0, uint64_t *out) {
+    if (n <= 0) return -1;
+    IntQuantization quant = { .X0 = x0, .X1 = 0 };
+    QField qf;
+    memset(&qf, 0, sizeof(qf));
+    qf.Hd.FieldCode = field_Unsi;
+    qf.Hd.ParticleLen = n;
+    qf.Data = (uint64_t *)q;
+    qf.Quant = &quant;
+    Field f = quant_Field(qf);
+    memcpy(out, f.Data, (size_t)n * sizeof(uint64_t));
+    free(f.Data);
+    return 0;
+}

@@ -15,6 +15,9 @@ ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 FIELD_POSN = 0x506F736E
 FIELD_VELC = 0x56656C63
+FIELD_PTID = 0x50746964
+FIELD_UNSI = 0x556E7369
+WIDTH_DAMAGED = 0xFFFFFFFF
 ALGO_DIFF = 0x44696666
 BLOCK_LEN = 1024
 
@@ -76,6 +79,20 @@ def _bind(lib):
                                            C.c_float, C.c_int, C.POINTER(C.c_int64)]),
         "orc_bench_decode": (C.c_double, [C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int32,
                                            C.c_int64, C.c_int]),
+        "orc_dequantize_field": (C.c_int, [C.c_void_p, _u64p, _f32p]),
+        "orc_id_quantize": (C.c_int, [_u64p, C.c_int32, C.c_uint64, _u64p, _u64p, _u64p]),
+        "orc_id_dequantize": (C.c_int, [_u64p, C.c_int32, C.c_uint64, _u64p, _u64p]),
+        "orc_uint_quantize": (C.c_int, [_u64p, C.c_int32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), _u64p]),
+        "orc_uint_dequantize": (C.c_int, [_u64p, C.c_int32, C.c_uint64, _u64p]),
+        "orc_diff_encode_id_field": (C.c_int64, [_u64p, C.c_int32, C.c_uint64, _u8p, C.c_int64]),
+        "orc_diff_decode_id_field": (C.c_int, [_u8p, C.c_int64, _u64p]),
+        "orc_diff_encode_uint_field": (C.c_int64, [_u64p, C.c_int32, _u8p, C.c_int64]),
+        "orc_diff_decode_uint_field": (C.c_int, [_u8p, C.c_int64, C.c_int32, _u64p]),
+        "orc_seg_field_blocks": (C.c_int64, [C.c_void_p]),
+        "orc_seg_bytes_bound": (C.c_int64, [C.c_void_p, C.c_int32]),
+        "orc_seg_to_bytes": (C.c_int64, [C.c_void_p, C.c_int32, C.c_int32, _u8p, C.c_int64]),
+        "orc_seg_from_bytes": (C.c_int32, [_u8p, C.c_int64, C.c_void_p, C.c_int32, C.POINTER(C.c_int32),
+                                            C.POINTER(C.c_int32)]),
         "orc_gen_zeldovich": (C.c_int, [C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64, C.c_float,
                                         C.c_void_p, C.c_void_p, C.c_int]),
         "orc_flavour": (C.c_char_p, []),
@@ -85,6 +102,11 @@ def _bind(lib):
         fn.restype = res
         fn.argtypes = args
     return lib
+
+
+class SegField(C.Structure):  # OrcSegField
+    _fields_ = [("FieldCode", C.c_uint32), ("AlgoCode", C.c_uint32), ("AlgoVersion", C.c_uint32),
+                ("ParticleLen", C.c_int32), ("Data", C.c_void_p), ("DataLen", C.c_int64)]
 
 
 class Oracle:
@@ -206,6 +228,109 @@ class Oracle:
         if rc != 0:
             raise ValueError("oracle decode_q failed: %d" % rc)
         return q[:3 * n]
+
+    # ---- quantisers alone, integer fields, segment image ----
+    def dequantize_field(self, hd, q64):
+        hd = np.array([hd], dtype=HEADER_DTYPE)
+        n = int(hd[0]["ParticleLen"])
+        q64 = np.ascontiguousarray(q64, dtype=np.uint64)
+        out = np.zeros(max(3 * n, 1), np.float32)
+        rc = self.lib.orc_dequantize_field(hd.ctypes.data, q64 if q64.size else np.zeros(1, np.uint64), out)
+        if rc:
+            raise ValueError("orc_dequantize_field: %d" % rc)
+        return out[:3 * n]
+
+    def id_quantize(self, ids, width):
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        n = ids.size
+        x0, x1, q = np.zeros(3, np.uint64), np.zeros(3, np.uint64), np.zeros(3 * n, np.uint64)
+        rc = self.lib.orc_id_quantize(ids, n, width, x0, x1, q)
+        if rc:
+            raise ValueError("orc_id_quantize: %d" % rc)
+        return x0, x1, q
+
+    def id_dequantize(self, q, width, x0):
+        q = np.ascontiguousarray(q, dtype=np.uint64)
+        n = q.size // 3
+        ids = np.zeros(n, np.uint64)
+        rc = self.lib.orc_id_dequantize(q, n, width, np.ascontiguousarray(x0, dtype=np.uint64), ids)
+        if rc:
+            raise ValueError("orc_id_dequantize: %d" % rc)
+        return ids
+
+    def uint_quantize(self, data):
+        data = np.ascontiguousarray(data, dtype=np.uint64)
+        x0, x1 = C.c_uint64(), C.c_uint64()
+        q = np.zeros(data.size, np.uint64)
+        rc = self.lib.orc_uint_quantize(data, data.size, C.byref(x0), C.byref(x1), q)
+        if rc:
+            raise ValueError("orc_uint_quantize: %d" % rc)
+        return x0.value, x1.value, q
+
+    def encode_id_field(self, ids, width):
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        cap = self.lib.orc_diff_bound(ids.size)
+        out = np.zeros(cap, np.uint8)
+        nbytes = self.lib.orc_diff_encode_id_field(ids if ids.size else np.zeros(1, np.uint64), ids.size, width, out, cap)
+        if nbytes < 0:
+            raise ValueError("orc_diff_encode_id_field: %d" % nbytes)
+        return out[:nbytes].copy()
+
+    def decode_id_field(self, payload):
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        n = int(parse_header(payload)["ParticleLen"])
+        ids = np.zeros(max(n, 1), np.uint64)
+        rc = self.lib.orc_diff_decode_id_field(payload, payload.size, ids)
+        if rc:
+            raise ValueError("orc_diff_decode_id_field: %d" % rc)
+        return ids[:n]
+
+    def encode_uint_field(self, data):
+        data = np.ascontiguousarray(data, dtype=np.uint64)
+        cap = self.lib.orc_diff_bound((data.size + 2) // 3)
+        out = np.zeros(cap, np.uint8)
+        nbytes = self.lib.orc_diff_encode_uint_field(data if data.size else np.zeros(1, np.uint64), data.size, out, cap)
+        if nbytes < 0:
+            raise ValueError("orc_diff_encode_uint_field: %d" % nbytes)
+        return out[:nbytes].copy()
+
+    def decode_uint_field(self, payload, n):
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        out = np.zeros(max(n, 1), np.uint64)
+        rc = self.lib.orc_diff_decode_uint_field(payload, payload.size, n, out)
+        if rc:
+            raise ValueError("orc_diff_decode_uint_field: %d" % rc)
+        return out[:n]
+
+    def seg_to_bytes(self, fields, particle_num):
+        """fields: [(field_code, particle_len, payload uint8 array)] -> segment image."""
+        arr = (SegField * len(fields))()
+        keep = []
+        for i, (code, n, payload) in enumerate(fields):
+            payload = np.ascontiguousarray(payload, dtype=np.uint8)
+            keep.append(payload)
+            arr[i] = SegField(code, ALGO_DIFF, 0x00000900, n, payload.ctypes.data, payload.size)
+        cap = self.lib.orc_seg_bytes_bound(arr, len(fields))
+        out = np.zeros(cap, np.uint8)
+        nbytes = self.lib.orc_seg_to_bytes(arr, len(fields), particle_num, out, cap)
+        if nbytes < 0:
+            raise ValueError("orc_seg_to_bytes: %d" % nbytes)
+        return out[:nbytes].copy()
+
+    def seg_from_bytes(self, image, max_fields=64):
+        """-> ([(field_code, particle_len, payload copy, valid)], particle_num); the image is not modified."""
+        buf = np.array(image, dtype=np.uint8, copy=True)
+        arr = (SegField * max_fields)()
+        valid = (C.c_int32 * max_fields)()
+        pn = C.c_int32()
+        nf = self.lib.orc_seg_from_bytes(buf, buf.size, arr, max_fields, valid, C.byref(pn))
+        if nf < 0:
+            raise ValueError("orc_seg_from_bytes: %d" % nf)
+        out = []
+        for i in range(nf):
+            off = arr[i].Data - buf.ctypes.data
+            out.append((arr[i].FieldCode, arr[i].ParticleLen, buf[off:off + arr[i].DataLen].copy(), bool(valid[i])))
+        return out, pn.value
 
     def gen_zeldovich(self, ngrid, box, seed, first_id, count, noise_cells=0.0, threads=1):
         """Host twin of the device generator's recipe (not bit-identical): (pos[3*count], vel[3*count])."""
