@@ -51,12 +51,31 @@ typedef struct MnwDiffBlock { /* 16 bytes per block, table follows the header */
     uint32_t Offset16;
 } MnwDiffBlock;
 
+#define MNWCUDA_WIDTH_DAMAGED 0xffffffffu /* MnwDiffBlock.Width of a block whose
+                                             checksum failed (segment image) */
+
+/* Integer fields (field_Ptid, field_Unsi) use the same 64-byte header: Width and
+ * X0[] / X1[] hold uint32 bit patterns -- Ptid: IDQuantization.Width, X0[3],
+ * X1[3] (src/types.h:97-99); Unsi: X0[0..1] / X1[0..1] = low, high word of
+ * IntQuantization.X0 / X1 (src/types.h:77-79) -- Depth = bit length of the
+ * widest range (at most 24), DitherSeed = 0. An Unsi field of N values is coded
+ * as three runs of ceil(N/3) (the tail repeats the last value): the payload
+ * header's ParticleLen is the run length, CField.Hd.ParticleLen stays N. */
+
+/* BlockHeader of a segment image (doc/header_format/header_format.tex:182-185) */
+typedef struct MnwBlockHeader {
+    int32_t  Length;
+    uint32_t Checksum; /* util_Checksum, src/util.c:438-445 (start value 1) */
+} MnwBlockHeader;
+
 /* ---- one field of a batch (host array) ---- */
 typedef struct MnwFieldDesc {
     int64_t  Offset;     /* encode: first float of the field's 3N planar input
                             inside d_in; decode: same inside d_out */
     int32_t  ParticleLen;
-    uint32_t FieldCode;  /* field_Posn or field_Velc (src/types.h:8-9) */
+    uint32_t FieldCode;  /* field_Posn or field_Velc (src/types.h:8-9); decode and
+                            the block-header calls also take field_Ptid /
+                            field_Unsi (ParticleLen = the run length for Unsi) */
     float    Delta;      /* Position/VelocityAccuracy.Delta (types.h:42-55) */
     float    Width;      /* PositionAccuracy.Width; ignored for Velc */
     uint64_t DitherSeed; /* recorded in the header; the decoder's rand_Seed seed
@@ -109,7 +128,8 @@ int64_t mnwcuda_LaunchCount(const MnwCudaCtx *ctx);
 /* Per-kernel device times of the most recent Encode/DecodeFieldsDev call
  * (bench bookkeeping; CUDA events on the call's stream, off by default).
  * ms[0] = k_encode (min/max + quantise + delta + pack, fused), ms[1] =
- * k_finalize + k_tables, ms[2..3] unused; ms[4..6] = k_parse_headers, k_stream_states,
+ * k_finalize + k_tables, ms[2] = k_block_headers (mnwcuda_BlockHeadersDev),
+ * ms[3] unused; ms[4..6] = k_parse_headers, k_stream_states,
  * k_unpack_dequant; -1 = not run. */
 void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on);
 int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms /* [7] */);
@@ -146,6 +166,61 @@ void *MnwCudaDAlloc_v0_9(void);
 void MnwCudaDFree_v0_9(void *buffer);
 /* Dither seed used by EncodeField / Compress on this buffer (default 0). */
 void mnwcuda_SetDitherSeed(void *buffer, uint64_t seed);
+/* CAlloc / DAlloc hand out pooled contexts (a context costs device allocations,
+ * streams and a jump table: the reference makes one Compressor per field,
+ * src/funcs.c:145-158). Acquire / Release are the same pool for other callers. */
+MnwCudaCtx *mnwcuda_Acquire(int device);
+void mnwcuda_Release(MnwCudaCtx *ctx);
+
+/* ---- the quantiser alone: quant_QField / quant_Field (src/quant.h:6-7) as the
+ * reference intends them (src/quant.c:161-327, 373-398, 451-608), with the fixes
+ * of DESIGN.md section 2: 3N outputs, the Quantization attached to the QField
+ * (the reference forgets to), dx = maxDiff, explicit dither seed. Posn, Velc,
+ * Ptid, Unsi. Data / Quant / Acc of the results are malloc'd (quant_FreeQField /
+ * quant_FreeField, src/quant.c:65-113). mnwcuda_DequantizeField dithers with the
+ * seed of the payload the QField came from when it was made by
+ * MnwCudaDecompress_v0_9 (remembered per Quant pointer until then), else with
+ * the buffer's seed: quant_Field(DFunc(cf)) == mnwcuda_DecodeField(cf). ---- */
+QField mnwcuda_QuantizeField(Field f, void *buffer);
+Field mnwcuda_DequantizeField(QField qf, void *buffer);
+void mnwcuda_ForgetQuant(const void *quant); /* a QField freed without being dequantised */
+
+/* ---- checksums and the segment image (doc/header_format/header_format.tex:
+ * 129-204): SegmentHeader | FieldHeader[F] | BlockHeader[B] | blocks. Blocks of
+ * an algo_Diff field: block 0 = its 64-byte header + block table, then one per
+ * packed block in table order (all multiples of 16 bytes). FieldHeader is the
+ * code's struct (src/types.h:103-108, 4th word ParticleLen). util_Checksum runs
+ * on the device, one thread per block. ---- */
+int64_t mnwcuda_BlockCount(const MnwFieldDesc *h_fields, int64_t nFields);
+/* d_headers[mnwcuda_BlockCount] <- {Length, Checksum} of every block of a packed
+ * stream on the device (the output of mnwcuda_EncodeFieldsDev) */
+int mnwcuda_BlockHeadersDev(MnwCudaCtx *ctx, const uint8_t *d_stream,
+                            const uint64_t *d_offsets, const MnwFieldDesc *h_fields,
+                            int64_t nFields, MnwBlockHeader *d_headers, void *stream);
+/* The inverse check: a packed block that does not match its header gets Width =
+ * MNWCUDA_WIDTH_DAMAGED in the stream's table (the decoders then return NaN /
+ * all-ones for its particles only, tex:188-196); d_fieldValid[f] = 0 when a
+ * field's block 0 is damaged (else 1). */
+int mnwcuda_VerifyBlocksDev(MnwCudaCtx *ctx, uint8_t *d_stream,
+                            const uint64_t *d_offsets, const MnwFieldDesc *h_fields,
+                            int64_t nFields, const MnwBlockHeader *d_headers,
+                            int32_t *d_fieldValid, void *stream);
+/* util_Checksum of nRanges byte ranges of a host buffer (copied to the device):
+ * h_sums[r] = checksum(h_data + h_off[r], h_len[r]). E.g. CField.Checksum of
+ * every field of a segment at once (src/funcs.c:72). */
+int mnwcuda_ChecksumsHost(MnwCudaCtx *ctx, const uint8_t *h_data, int64_t dataLen,
+                          const int64_t *h_off, const int64_t *h_len, int64_t nRanges,
+                          uint32_t *h_sums);
+/* CSeg <-> segment image. ToImage returns the bytes written (<= ImageBound) or
+ * <0; FromImage fills fields[0..F) (Data malloc'd, Checksum = util_Checksum of
+ * the payload as received), valid[f] = 0 for a field whose block 0 is damaged,
+ * returns F or <0 (-4: the segment header's own checksum failed). */
+int64_t mnwcuda_SegmentImageBound(const CField *fields, int32_t nFields);
+int64_t mnwcuda_SegmentToImage(MnwCudaCtx *ctx, const CField *fields, int32_t nFields,
+                               int32_t particleNum, uint8_t *h_image, int64_t cap);
+int32_t mnwcuda_SegmentFromImage(MnwCudaCtx *ctx, const uint8_t *h_image, int64_t len,
+                                 CField *fields, int32_t maxFields, int32_t *valid,
+                                 int32_t *particleNum);
 
 /* ---- synthetic input (bench/tests): Zel'dovich-displaced Lagrangian grid,
  * ids [firstId, firstId+count) of an ngrid^3 box, planar float32.

@@ -77,6 +77,21 @@ CSeg MnwSeg_Encode(Seg s);
 Seg MnwSeg_Decode(CSeg cs);
 void MnwCSeg_Free(CSeg cs);
 void MnwSeg_Free(Seg s);
+/* ToBytes / FromBytes (src/funcs.c:78-120) as the segment image of
+ * doc/header_format/header_format.tex:129-204 (mnwcuda_SegmentToImage). A block
+ * whose checksum fails costs only its own particles (NaN / all ones after
+ * decoding); valid[f] = 0 (valid may be NULL) for a field whose header block is
+ * damaged; FieldLen = -1 when the segment header itself is. Data is malloc'd. */
+typedef struct MnwBytes { uint8_t *Data; int64_t Len; } MnwBytes;
+MnwBytes MnwSeg_ToBytes(CSeg cs, int32_t particleNum);
+CSeg MnwSeg_FromBytes(MnwBytes bytes, int32_t *valid, int32_t *particleNum);
+/* the reference's quantiser interface (src/quant.h:6-9) over the device kernels:
+ * what src/funcs.c's Quantize / UndoQuantize / Seg_Free / QSeg_Free call */
+QField quant_QField(Field f);
+Field quant_Field(QField qf);
+void quant_FreeQField(QField qf);
+void quant_FreeField(Field f);
+void MnwQuant_SetDitherSeed(uint64_t seed);
 /* util_Checksum (src/util.c:438-445): rotate right by one, add byte, start 1 */
 uint32_t MnwChecksum(const uint8_t *data, int64_t len);
 /* dither seed of the fields encoded by MnwSeg_Encode from now on (default 0) */

@@ -37,6 +37,20 @@ typedef struct VelocityAccuracy { /* types.h:48-55 */
     float SymLog10Threshold;
 } VelocityAccuracy;
 
+typedef struct IDAccuracy { /* types.h:57-59 */
+    uint64_t Width;           /* grid cells per side: id = ix + W*iy + W^2*iz */
+} IDAccuracy;
+
+typedef uint8_t IntAccuracy; /* types.h:40: does nothing */
+
+typedef struct IntQuantization { /* types.h:77-79 */
+    uint64_t X0, X1;
+} IntQuantization;
+
+typedef struct IDQuantization { /* types.h:97-99 */
+    uint64_t Width, X0[3], X1[3];
+} IDQuantization;
+
 typedef struct PositionQuantization { /* types.h:82-87 */
     uint8_t *Depths;
     int32_t Len;

@@ -23,6 +23,9 @@ HOST_LIB_PATH = os.path.join(_HERE, "libminnow_host.so")
 
 FIELD_POSN = 0x506F736E
 FIELD_VELC = 0x56656C63
+FIELD_PTID = 0x50746964
+FIELD_UNSI = 0x556E7369
+WIDTH_DAMAGED = 0xFFFFFFFF
 ALGO_DIFF = 0x44696666
 ALGO_VERSION = 0x00000900
 BLOCK_LEN = 1024
@@ -87,6 +90,22 @@ class VelocityQuantization(C.Structure):
                 ("Depth", C.c_uint8)]
 
 
+class IDAccuracy(C.Structure):
+    _fields_ = [("Width", C.c_uint64)]
+
+
+class IDQuantization(C.Structure):
+    _fields_ = [("Width", C.c_uint64), ("X0", C.c_uint64 * 3), ("X1", C.c_uint64 * 3)]
+
+
+class IntQuantization(C.Structure):
+    _fields_ = [("X0", C.c_uint64), ("X1", C.c_uint64)]
+
+
+class BlockHeader(C.Structure):
+    _fields_ = [("Length", C.c_int32), ("Checksum", C.c_uint32)]
+
+
 class FieldDesc(C.Structure):
     _fields_ = [("Offset", C.c_int64), ("ParticleLen", C.c_int32), ("FieldCode", C.c_uint32),
                 ("Delta", C.c_float), ("Width", C.c_float), ("DitherSeed", C.c_uint64)]
@@ -120,6 +139,22 @@ EXPORTS = {
     "mnwcuda_SetDitherSeed": (None, [C.c_void_p, C.c_uint64]),
     "mnwcuda_GenerateZeldovich": (C.c_int, [C.c_void_p, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64,
                                             C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mnwcuda_Acquire": (C.c_void_p, [C.c_int]),
+    "mnwcuda_Release": (None, [C.c_void_p]),
+    "mnwcuda_QuantizeField": (QField, [Field, C.c_void_p]),
+    "mnwcuda_DequantizeField": (Field, [QField, C.c_void_p]),
+    "mnwcuda_ForgetQuant": (None, [C.c_void_p]),
+    "mnwcuda_BlockCount": (C.c_int64, [C.POINTER(FieldDesc), C.c_int64]),
+    "mnwcuda_BlockHeadersDev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64,
+                                          C.c_void_p, C.c_void_p]),
+    "mnwcuda_VerifyBlocksDev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mnwcuda_ChecksumsHost": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                                        C.c_void_p]),
+    "mnwcuda_SegmentImageBound": (C.c_int64, [C.POINTER(CField), C.c_int32]),
+    "mnwcuda_SegmentToImage": (C.c_int64, [C.c_void_p, C.POINTER(CField), C.c_int32, C.c_int32, C.c_void_p, C.c_int64]),
+    "mnwcuda_SegmentFromImage": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(CField), C.c_int32,
+                                             C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "mnwcuda_GenerateZeldovichRough": (C.c_int, [C.c_void_p, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64,
                                                  C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
@@ -153,6 +188,14 @@ class CSeg(C.Structure):
     _fields_ = [("Fields", C.POINTER(CField)), ("FieldLen", C.c_int32)]
 
 
+class QSeg(C.Structure):
+    _fields_ = [("Fields", C.POINTER(QField)), ("FieldLen", C.c_int32)]
+
+
+class Bytes(C.Structure):  # MnwBytes
+    _fields_ = [("Data", C.c_void_p), ("Len", C.c_int64)]
+
+
 HOST_EXPORTS = {
     "Register_New": (Register, []),
     "Register_Free": (None, [Register]),
@@ -169,6 +212,13 @@ HOST_EXPORTS = {
     "MnwSeg_Free": (None, [Seg]),
     "MnwChecksum": (C.c_uint32, [C.c_void_p, C.c_int64]),
     "MnwSeg_SetDitherSeed": (None, [C.c_uint64]),
+    "MnwSeg_ToBytes": (Bytes, [CSeg, C.c_int32]),
+    "MnwSeg_FromBytes": (CSeg, [Bytes, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "quant_QField": (QField, [Field]),
+    "quant_Field": (Field, [QField]),
+    "quant_FreeQField": (None, [QField]),
+    "quant_FreeField": (None, [Field]),
+    "MnwQuant_SetDitherSeed": (None, [C.c_uint64]),
 }
 
 _lib = None
@@ -263,7 +313,7 @@ class Codec:
         return lib().mnwcuda_LaunchCount(self.ctx)
 
     # mnwcuda_KernelTimes slots; None = not used by this version of the library
-    KERNEL_NAMES = ("k_encode", "k_finalize+k_tables", None, None,
+    KERNEL_NAMES = ("k_encode", "k_finalize+k_tables", "k_block_headers", None,
                     "k_parse_headers", "k_stream_states", "k_unpack_dequant")
 
     def enable_kernel_timing(self, on=True):
@@ -350,6 +400,81 @@ class Codec:
         _libc.free(f.Acc)
         return out, delta
 
+    # ---- quantiser alone and integer fields ----
+    def _field(self, field_code, data, delta=0.0, width=0.0):
+        """(Field, keep-alive objects) for a host array"""
+        if field_code in (FIELD_POSN, FIELD_VELC):
+            data = np.ascontiguousarray(data, dtype=np.float32).reshape(-1)
+            n = data.size // 3
+            acc = PositionAccuracy(None, delta, width, 0) if field_code == FIELD_POSN else \
+                VelocityAccuracy(None, delta, 0, 0, 0.0)
+        else:
+            data = np.ascontiguousarray(data, dtype=np.uint64).reshape(-1)
+            n = data.size
+            acc = IDAccuracy(int(width)) if field_code == FIELD_PTID else C.c_uint8(0)
+        f = Field(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), 1, data.ctypes.data, C.addressof(acc))
+        return f, (data, acc)
+
+    def quantize_field(self, field_code, data, delta=0.0, width=0.0):
+        """mnwcuda_QuantizeField -> (q uint64 array, quant dict)"""
+        f, keep = self._field(field_code, data, delta, width)
+        qf = lib().mnwcuda_QuantizeField(f, self.ctx)
+        n = f.Hd.ParticleLen
+        count = n if field_code == FIELD_UNSI else 3 * n
+        q = np.ctypeslib.as_array(C.cast(qf.Data, C.POINTER(C.c_uint64)), shape=(count,)).copy() if count else \
+            np.zeros(0, np.uint64)
+        info = _quant_info(field_code, qf.Quant)
+        _libc.free(qf.Data)
+        _libc.free(qf.Quant)
+        return q, info
+
+    def dequantize_field(self, field_code, n, q64, info):
+        """mnwcuda_DequantizeField: (q, quant dict) -> field data (float32[3n] or uint64[n])"""
+        q64 = np.ascontiguousarray(q64, dtype=np.uint64)
+        quant = _quant_struct(field_code, info)
+        qf = QField(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), 1, q64.ctypes.data, C.addressof(quant))
+        f = lib().mnwcuda_DequantizeField(qf, self.ctx)
+        if field_code in (FIELD_POSN, FIELD_VELC):
+            out = np.ctypeslib.as_array(C.cast(f.Data, C.POINTER(C.c_float)), shape=(3 * n,)).copy() if n else \
+                np.zeros(0, np.float32)
+        else:
+            out = np.ctypeslib.as_array(C.cast(f.Data, C.POINTER(C.c_uint64)), shape=(n,)).copy() if n else \
+                np.zeros(0, np.uint64)
+        _libc.free(f.Data)
+        if f.Acc:
+            _libc.free(f.Acc)
+        return out
+
+    def encode_ints(self, field_code, data, width=0):
+        """mnwcuda_EncodeField for Ptid (width = grid cells per side) / Unsi -> payload bytes"""
+        f, keep = self._field(field_code, data, 0.0, width)
+        cf = lib().mnwcuda_EncodeField(f, self.ctx)
+        out = np.ctypeslib.as_array(C.cast(cf.Data, C.POINTER(C.c_uint8)), shape=(cf.DataLen,)).copy()
+        _libc.free(cf.Data)
+        return out
+
+    def decode_ints(self, field_code, n, payload):
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        cf = CField(FieldHeader(field_code, ALGO_DIFF, ALGO_VERSION, n), payload.ctypes.data, payload.size, 0)
+        f = lib().mnwcuda_DecodeField(cf, self.ctx)
+        out = np.ctypeslib.as_array(C.cast(f.Data, C.POINTER(C.c_uint64)), shape=(n,)).copy() if n else \
+            np.zeros(0, np.uint64)
+        _libc.free(f.Data)
+        if f.Acc:
+            _libc.free(f.Acc)
+        return out
+
+    def block_headers_dev(self, d_stream, d_offsets, descs, n_fields, stream=None):
+        """mnwcuda_BlockHeadersDev -> torch tensor of int32 pairs [nBlocks, 2] on the device"""
+        import torch
+        nblk = lib().mnwcuda_BlockCount(descs, n_fields)
+        d_hdr = torch.empty((nblk, 2), dtype=torch.int32, device=d_stream.device)
+        rc = lib().mnwcuda_BlockHeadersDev(self.ctx, d_stream.data_ptr(), d_offsets.data_ptr(), descs, n_fields,
+                                           d_hdr.data_ptr(), _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwcuda_BlockHeadersDev: %d" % rc)
+        return d_hdr
+
     def compress(self, field_code, q64, x0, x1, depth, width=0.0):
         """MnwCudaCompress_v0_9: the literal CFunc(QField) boundary."""
         q64 = np.ascontiguousarray(q64, dtype=np.uint64)
@@ -379,6 +504,32 @@ class Codec:
         _libc.free(qf.Data)
         _libc.free(qf.Quant)
         return q, info
+
+
+def _quant_info(field_code, ptr):
+    if field_code == FIELD_POSN:
+        q = C.cast(ptr, C.POINTER(PositionQuantization)).contents
+        return {"X0": list(q.X0), "X1": list(q.X1), "Depth": int(q.Depth), "Width": float(q.Width)}
+    if field_code == FIELD_VELC:
+        q = C.cast(ptr, C.POINTER(VelocityQuantization)).contents
+        return {"X0": list(q.X0), "X1": list(q.X1), "Depth": int(q.Depth)}
+    if field_code == FIELD_PTID:
+        q = C.cast(ptr, C.POINTER(IDQuantization)).contents
+        return {"X0": list(q.X0), "X1": list(q.X1), "Width": int(q.Width)}
+    q = C.cast(ptr, C.POINTER(IntQuantization)).contents
+    return {"X0": int(q.X0), "X1": int(q.X1)}
+
+
+def _quant_struct(field_code, info):
+    if field_code == FIELD_POSN:
+        return PositionQuantization(None, 0, info["Width"], (C.c_float * 3)(*info["X0"]), (C.c_float * 3)(*info["X1"]),
+                                    info["Depth"])
+    if field_code == FIELD_VELC:
+        return VelocityQuantization(None, 0, 0, (C.c_float * 3)(*info["X0"]), (C.c_float * 3)(*info["X1"]), 0.0,
+                                    info["Depth"])
+    if field_code == FIELD_PTID:
+        return IDQuantization(info["Width"], (C.c_uint64 * 3)(*info["X0"]), (C.c_uint64 * 3)(*info["X1"]))
+    return IntQuantization(info["X0"], info["X1"])
 
 
 def _host_ptr(a):

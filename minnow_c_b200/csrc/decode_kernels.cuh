@@ -28,6 +28,7 @@ struct DecodeParams {
 };
 
 constexpr int kJumpPows = 26;
+constexpr uint32_t kWidthDamaged = 0xffffffffu;  // table entry of a block whose checksum failed (k_block_headers)
 
 // ---------------------------------------------------------------------------
 // K3p: one thread per field reads the 64-byte header: quantisation parameters,
@@ -305,8 +306,11 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
             const int gl = g0 + lane;
             const int compL = gl / fd.nb;
             const int lenL = min(kBlockLen, fd.n - (gl - compL * fd.nb) * kBlockLen);
+            // (a block whose checksum failed upstream is marked, not read: its values come out as NaN)
+            const bool damaged = ent.z == kWidthDamaged;
+            if (damaged) ent.z = 0u;
             const int size16L = (((lenL * (int)ent.z + 31) >> 5) + 3) >> 2;
-            bad = ent.z > (uint32_t)kMaxWidth || (int64_t)ent.w + size16L > payloadLen16;
+            bad = ent.z > (uint32_t)kMaxWidth || (!damaged && (int64_t)ent.w + size16L > payloadLen16);
             x0L = compL == 0 ? qp.X0[0] : compL == 1 ? qp.X0[1] : qp.X0[2];
             // Can util_Periodic move any value of this component? The values are
             // x0 + bw*q + dither with q up to the index of X1 (the component's own
@@ -317,7 +321,7 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
             float top = __fadd_rn(x1L, __fadd_rn(bw, bw));
             top = __fadd_rn(top, __fmul_rn(fabsf(top), 9.5367431640625e-07f));
             const bool inBox = x0L >= 0.0f && top < L;
-            ent.z |= (uint32_t)compL << 8 | (isPos && !inBox ? 1u << 10 : 0u);
+            ent.z |= (uint32_t)compL << 8 | (isPos && !inBox ? 1u << 10 : 0u) | (damaged ? 1u << 11 : 0u);
         }
         if (__any_sync(0xffffffffu, bad)) {
             if (lane == 0) atomicCAS(p.error, 0, kErrPayload);
@@ -336,6 +340,21 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         const int b = g0 + k - comp * fd.nb;
         const int len = min(kBlockLen, fd.n - b * kBlockLen);
         const int size16 = (((len * w + 31) >> 5) + 3) >> 2;
+
+        if (zz & (1u << 11)) {
+            // damaged block: NaN (all ones at the DFunc boundary) for its values; the lane's
+            // stream still advances by its share, so the task's other blocks are untouched
+            const int mine = min(max(len - lane * kChunk, 0), kChunk);
+            if (kToQ) {
+                uint64_t *dstq = p.qOut + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
+                for (int el = lane; el < len; el += 32) dstq[el] = ~0ull;
+            } else {
+                for (int i = 0; i < mine; i++) (void)xs128p_next(s0, s1);
+                float *dstf = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
+                for (int el = lane; el < len; el += 32) dstf[el] = __int_as_float(0x7fc00000);
+            }
+            continue;
+        }
 
         // ---- unpack ----
         const uint4 *src = payload + off16;

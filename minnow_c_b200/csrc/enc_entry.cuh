@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(128) k_finalize(EncodeParams p, int64_t fixedT
     h.ParticleLen = fd.n;
     h.Depth = (uint8_t)qp.depth;
     h.Pad[0] = h.Pad[1] = h.Pad[2] = 0;
-    h.Width = fd.fieldCode == field_Posn ? fd.width : 0.0f;
+    h.Width = (fd.fieldCode == field_Posn || fd.fieldCode == field_Ptid) ? fd.width : 0.0f;  // (Ptid: uint32 bits)
     for (int c = 0; c < 3; c++) { h.X0[c] = qp.X0[c]; h.X1[c] = qp.X1[c]; }
     h.BlockLen = kBlockLen;
     h.DitherRun = MNWCUDA_DITHER_RUN;

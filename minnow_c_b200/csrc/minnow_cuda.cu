@@ -11,12 +11,15 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <unordered_map>
 #include <vector>
 
 #include "minnow_cuda.h"
 #include "decode_kernels.cuh"
 #include "enc_kernel.cuh"
 #include "gen_kernels.cuh"
+#include "quant_kernels.cuh"
 
 using namespace mnw;
 
@@ -68,7 +71,7 @@ struct MnwCudaCtx {
     int64_t launches = 0;
     uint64_t ditherSeed = 0;
     Scratch fields, quant, minmax, tileState, seeds, tableOf, states, misc, ring;
-    Scratch ioA, ioB, ioC;  // host-buffer entry points: device staging
+    Scratch ioA, ioB, ioC, ioD;  // host-buffer entry points: device staging
     Scratch jumpTab;        // columns of J^k for k < tabStreams (k_jump_table), built on first use
     int64_t tabStreams = 0;
     cudaEvent_t tabEv = nullptr;
@@ -211,7 +214,7 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaDeviceSynchronize();
     Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->seeds,
                       &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC,
-                      &ctx->jumpTab};
+                      &ctx->ioD, &ctx->jumpTab};
     for (Scratch *s : all) s->release();
     cudaFree(ctx->jumpPow);
     cudaFree(ctx->error);
@@ -251,12 +254,12 @@ extern "C" void mnwcuda_EnableKernelTiming(MnwCudaCtx *ctx, int on) {
             if (!e) CUDA_CHECK(cudaEventCreate(&e));
 }
 
-// ms[0..1] = k_encode (+k_depth_empty), k_finalize; ms[2..3] unused (-1)
+// ms[0..1] = k_encode (+k_depth_empty), k_finalize; ms[2] = k_block_headers (mnwcuda_BlockHeadersDev); ms[3] unused (-1)
 // ms[4..6] = k_parse_headers, k_stream_states, k_unpack_dequant
 extern "C" int mnwcuda_KernelTimes(MnwCudaCtx *ctx, float *ms) {
     if (!ctx->timing) return -1;
     CUDA_CHECK(cudaSetDevice(ctx->device));
-    static const int first[7] = {0, 1, -1, -1, 5, 6, 7};
+    static const int first[7] = {0, 1, 3, -1, 5, 6, 7};
     for (int k = 0; k < 7; k++) {
         int a = first[k], b = a + 1;
         ms[k] = -1.0f;
@@ -333,7 +336,9 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
     for (int64_t i = 0; i < nFields; i++) {
         const MnwFieldDesc &d = h[i];
         if (d.ParticleLen < 0 || d.Offset < 0) return -1;
-        if (d.FieldCode != field_Posn && d.FieldCode != field_Velc) return -3;
+        if (d.FieldCode != field_Posn && d.FieldCode != field_Velc && d.FieldCode != field_Ptid &&
+            d.FieldCode != field_Unsi)
+            return -3;
         DevField &f = pl.fields[(size_t)i];
         f.ioOff = d.Offset;
         f.fixedBase = pl.fixedTotal;
@@ -492,6 +497,8 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     Plan pl;
     int rc = build_plan(h_fields, nFields, pl);
     if (rc) return rc;
+    for (int64_t i = 0; i < nFields; i++)  // float fields only: integer fields go through mnwcuda_EncodeField
+        if (h_fields[i].FieldCode != field_Posn && h_fields[i].FieldCode != field_Velc) return -3;
     EncodeParams p = prepare_encode(ctx, pl, d_out, outCap, d_offsets, s);
     p.in = d_in;
     // the B work of a block trails its A work by one (largest) field plus what can be in flight
@@ -525,6 +532,8 @@ extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, con
     Plan pl;
     int rc = build_plan(h_fields, nFields, pl);
     if (rc) return rc;
+    for (int64_t i = 0; i < nFields; i++)  // float fields only: integer fields go through mnwcuda_DecodeField
+        if (h_fields[i].FieldCode != field_Posn && h_fields[i].FieldCode != field_Velc) return -3;
     const size_t nF = (size_t)nFields;
     DecodeParams p;
     memset(&p, 0, sizeof(p));
@@ -635,10 +644,14 @@ extern "C" void mnwcuda_SetDitherSeed(void *buffer, uint64_t seed) {
     static_cast<MnwCudaCtx *>(buffer)->ditherSeed = seed;
 }
 
+static CField encode_int_field(Field f, MnwCudaCtx *ctx);   // minnow_ext.inl: Ptid / Unsi
+static Field decode_int_field(CField cf, MnwCudaCtx *ctx);
+
 extern "C" CField mnwcuda_EncodeField(Field f, void *buffer) {
     MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
     if (!ctx) MNW_PANIC("mnwcuda_EncodeField needs the buffer returned by MnwCudaCAlloc_v0_9.");
     CUDA_CHECK(cudaSetDevice(ctx->device));
+    if (f.Hd.FieldCode == field_Ptid || f.Hd.FieldCode == field_Unsi) return encode_int_field(f, ctx);
     MnwFieldDesc d;
     memset(&d, 0, sizeof(d));
     d.ParticleLen = f.Hd.ParticleLen;
@@ -665,6 +678,7 @@ extern "C" Field mnwcuda_DecodeField(CField cf, void *buffer) {
     MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
     if (!ctx) MNW_PANIC("mnwcuda_DecodeField needs the buffer returned by MnwCudaDAlloc_v0_9.");
     CUDA_CHECK(cudaSetDevice(ctx->device));
+    if (cf.Hd.FieldCode == field_Ptid || cf.Hd.FieldCode == field_Unsi) return decode_int_field(cf, ctx);
     if (cf.Hd.ParticleLen < 0 || cf.DataLen < mnwcuda_FieldFixedBytes(cf.Hd.ParticleLen))
         MNW_PANIC("mnwcuda_DecodeField: payload too short.");
     MnwDiffHeader h;
@@ -881,138 +895,7 @@ extern "C" int mnwcuda_DecodeFieldsHost(MnwCudaCtx *ctx, const uint8_t *h_in, co
     return err ? -100 - err : 0;
 }
 
-// ---------------------------------------------------------------------------
-// the six plugin functions (src/register.h:15-22): literal QField <-> CField
-// ---------------------------------------------------------------------------
-extern "C" void *MnwCudaCAlloc_v0_9(void) { return mnwcuda_Create(-1); }
-extern "C" void MnwCudaCFree_v0_9(void *buffer) { mnwcuda_Destroy(static_cast<MnwCudaCtx *>(buffer)); }
-extern "C" void *MnwCudaDAlloc_v0_9(void) { return mnwcuda_Create(-1); }
-extern "C" void MnwCudaDFree_v0_9(void *buffer) { mnwcuda_Destroy(static_cast<MnwCudaCtx *>(buffer)); }
-
-extern "C" CField MnwCudaCompress_v0_9(QField qf, void *buffer) {
-    MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
-    if (!ctx) MNW_PANIC("MnwCudaCompress_v0_9 needs the buffer returned by MnwCudaCAlloc_v0_9.");
-    if (!qf.Quant) MNW_PANIC("QField.Quant is NULL: the quantizer must attach its Quantization.");
-    CUDA_CHECK(cudaSetDevice(ctx->device));
-    cudaStream_t s = ctx->own;
-    MnwFieldDesc d;
-    memset(&d, 0, sizeof(d));
-    d.ParticleLen = qf.Hd.ParticleLen;
-    d.FieldCode = qf.Hd.FieldCode;
-    d.DitherSeed = ctx->ditherSeed;
-    DevQuant dq;
-    memset(&dq, 0, sizeof(dq));
-    if (qf.Hd.FieldCode == field_Posn) {
-        const PositionQuantization *q = static_cast<const PositionQuantization *>(qf.Quant);
-        if (q->Depths) MNW_PANIC("Per-particle depths are not supported by algo_Diff v0.9.");
-        d.Width = q->Width;
-        for (int c = 0; c < 3; c++) { dq.X0[c] = q->X0[c]; dq.X1[c] = q->X1[c]; }
-        dq.depth = q->Depth;
-    } else if (qf.Hd.FieldCode == field_Velc) {
-        const VelocityQuantization *q = static_cast<const VelocityQuantization *>(qf.Quant);
-        if (q->Depths) MNW_PANIC("Per-particle depths are not supported by algo_Diff v0.9.");
-        if (q->SymLog10Scaled) MNW_PANIC("symLog10 not supported.");
-        for (int c = 0; c < 3; c++) { dq.X0[c] = q->X0[c]; dq.X1[c] = q->X1[c]; }
-        dq.depth = q->Depth;
-    } else {
-        MNW_PANIC("Field code %x is not supported by algo_Diff v0.9.", qf.Hd.FieldCode);
-    }
-    if (dq.depth > 24) MNW_PANIC("Quantization depth %u exceeds 24.", dq.depth);
-    for (int c = 0; c < 3; c++)
-        if (dq.maxDiff < dq.X1[c] - dq.X0[c]) dq.maxDiff = dq.X1[c] - dq.X0[c];
-
-    Plan pl;
-    if (build_plan(&d, 1, pl)) MNW_PANIC("MnwCudaCompress_v0_9: bad field.");
-    const size_t inBytes = (size_t)d.ParticleLen * 3 * sizeof(uint64_t);
-    const int64_t cap = mnwcuda_FieldBound(d.ParticleLen);
-    uint64_t *d_q = static_cast<uint64_t *>(ctx->ioA.need(inBytes + 16));
-    uint8_t *d_out = static_cast<uint8_t *>(ctx->ioB.need((size_t)cap));
-    uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need(2 * sizeof(uint64_t)));
-    if (inBytes) CUDA_CHECK(cudaMemcpyAsync(d_q, qf.Data, inBytes, cudaMemcpyHostToDevice, s));
-    EncodeParams p = prepare_encode(ctx, pl, d_out, cap, d_off, s);
-    CUDA_CHECK(cudaMemcpyAsync(p.quant, &dq, sizeof(dq), cudaMemcpyHostToDevice, s));
-    if (pl.nBlocks > 0) {
-        p.nGroups = (pl.nBlocks + kGroupSlots - 1) / kGroupSlots;
-        p.qIn = d_q;
-        launch_encode(ctx, p, pl.floatEnd, true, s);
-    }
-    launch_finalize(ctx, pl, p, s);
-    panic_on_status(ctx, s, "MnwCudaCompress_v0_9");
-    CField cf;
-    memset(&cf, 0, sizeof(cf));
-    cf.Hd = qf.Hd;
-    cf.Data = fetch_payload(ctx, d_out, d_off, &cf.DataLen);
-    return cf;
-}
-
-extern "C" QField MnwCudaDecompress_v0_9(CField cf, void *buffer) {
-    MnwCudaCtx *ctx = static_cast<MnwCudaCtx *>(buffer);
-    if (!ctx) MNW_PANIC("MnwCudaDecompress_v0_9 needs the buffer returned by MnwCudaDAlloc_v0_9.");
-    if (cf.Hd.ParticleLen < 0 || cf.DataLen < mnwcuda_FieldFixedBytes(cf.Hd.ParticleLen))
-        MNW_PANIC("MnwCudaDecompress_v0_9: payload too short.");
-    CUDA_CHECK(cudaSetDevice(ctx->device));
-    cudaStream_t s = ctx->own;
-    MnwDiffHeader h;
-    memcpy(&h, cf.Data, sizeof(h));
-    MnwFieldDesc d;
-    memset(&d, 0, sizeof(d));
-    d.ParticleLen = cf.Hd.ParticleLen;
-    d.FieldCode = cf.Hd.FieldCode;
-    Plan pl;
-    if (build_plan(&d, 1, pl)) MNW_PANIC("MnwCudaDecompress_v0_9: bad field.");
-    const size_t outBytes = (size_t)d.ParticleLen * 3 * sizeof(uint64_t);
-    uint8_t *d_in = static_cast<uint8_t *>(ctx->ioB.need((size_t)cf.DataLen + 16));
-    uint64_t *d_q = static_cast<uint64_t *>(ctx->ioA.need(outBytes + 16));
-    uint64_t *d_off = static_cast<uint64_t *>(ctx->ioC.need(2 * sizeof(uint64_t)));
-    uint64_t off[2] = {0, (uint64_t)cf.DataLen};
-    CUDA_CHECK(cudaMemcpyAsync(d_in, cf.Data, (size_t)cf.DataLen, cudaMemcpyHostToDevice, s));
-    CUDA_CHECK(cudaMemcpyAsync(d_off, off, sizeof(off), cudaMemcpyHostToDevice, s));
-    DecodeParams p;
-    memset(&p, 0, sizeof(p));
-    p.in = d_in;
-    p.offsets = d_off;
-    p.fields = static_cast<DevField *>(ctx->fields.need(sizeof(DevField)));
-    p.nFields = 1;
-    p.uniformTasks = pl.uniformTasks;
-    p.quant = static_cast<DevQuant *>(ctx->quant.need(sizeof(DevQuant)));
-    p.seeds = static_cast<uint64_t *>(ctx->seeds.need(sizeof(uint64_t)));
-    p.tableOf = static_cast<int *>(ctx->tableOf.need(sizeof(int)));
-    p.maxStreams = pl.maxStreams;
-    p.jumpPow = ctx->jumpPow;
-    p.qOut = d_q;
-    p.error = ctx->error;
-    CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), sizeof(DevField),
-                               cudaMemcpyHostToDevice, s));
-    k_parse_headers<<<1, 128, 0, s>>>(p);
-    ctx->launches++;
-    if (pl.nTasks > 0) {
-        k_unpack_dequant<true><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
-            p, pl.nTasks);
-        ctx->launches++;
-    }
-    CUDA_CHECK(cudaGetLastError());
-    panic_on_status(ctx, s, "MnwCudaDecompress_v0_9");
-
-    QField qf;
-    memset(&qf, 0, sizeof(qf));
-    qf.Hd = cf.Hd;
-    qf.Data = static_cast<uint64_t *>(xmalloc(outBytes));
-    if (outBytes) CUDA_CHECK(cudaMemcpyAsync(qf.Data, d_q, outBytes, cudaMemcpyDeviceToHost, s));
-    CUDA_CHECK(cudaStreamSynchronize(s));
-    if (cf.Hd.FieldCode == field_Posn) {
-        PositionQuantization *q = static_cast<PositionQuantization *>(calloc(1, sizeof(*q)));
-        q->Width = h.Width;
-        for (int c = 0; c < 3; c++) { q->X0[c] = h.X0[c]; q->X1[c] = h.X1[c]; }
-        q->Depth = h.Depth;
-        qf.Quant = q;
-    } else {
-        VelocityQuantization *q = static_cast<VelocityQuantization *>(calloc(1, sizeof(*q)));
-        for (int c = 0; c < 3; c++) { q->X0[c] = h.X0[c]; q->X1[c] = h.X1[c]; }
-        q->Depth = h.Depth;
-        qf.Quant = q;
-    }
-    return qf;
-}
+#include "minnow_ext.inl"
 
 // ---------------------------------------------------------------------------
 // synthetic input
