@@ -438,6 +438,10 @@ def run_b200(args):
         check["sample_bytes_vs_reference"] = shard_parity
         check["ok"] = bool(check["ok"] and shard_parity["ok"])
 
+    checksums = refflow = None
+    if n_gpus == 1 and not args.no_sweep:
+        checksums = run_checksums(torch, mc, codec, d_out, d_off, descs, nf, comp_bytes, peak)
+        refflow = run_reference_flow(torch, mc, d_in, seg, fields)
     sweep = None
     if n_gpus == 1 and not args.no_sweep:
         sweep = run_sweep(torch, mc, codec, d_in, d_out, d_off, d_dec, fields, seg, peak, ngrid, first_id, n_seg)
@@ -457,6 +461,10 @@ def run_b200(args):
     }
     if gather is not None:
         line["gather"] = gather
+    if checksums is not None:
+        line["checksums"] = checksums
+    if refflow is not None:
+        line["e2e_reference_flow"] = refflow
     if sweep is not None:
         line["sweep"] = sweep
     print(json.dumps(line), flush=True)
@@ -745,6 +753,96 @@ def run_sweep(torch, mc, codec, d_in, d_out, d_off, d_dec, fields, seg, peak, ng
     out["ok"] = all(r["ok"] for rows in out["fields"].values() for r in rows)
     generate(codec, d_in, ngrid, first_id, n_seg, seg)  # back to the headline's field
     torch.cuda.synchronize()
+    return out
+
+
+def run_checksums(torch, mc, codec, d_out, d_off, descs, nf, comp_bytes, peak):
+    """The segment image's BlockHeader table for the whole packed slab: util_Checksum
+    (/root/reference/src/util.c:438-445) of every block on the device, one thread per
+    block (untimed in the metric: the reference leaves checksums to the caller)."""
+    codec.enable_kernel_timing(True)
+    ms = []
+    for rep in range(4):
+        hdr = codec.block_headers_dev(d_out, d_off, descs, nf)
+        torch.cuda.synchronize()
+        if rep:
+            ms.append(codec.kernel_times()["k_block_headers"])
+    codec.enable_kernel_timing(False)
+    if codec.status() != 0:
+        raise SystemExit("device-side error in the block checksums")
+    t = float(np.mean(ms))
+    return {"kernel": "k_block_headers", "blocks": int(hdr.shape[0]), "ms": round(t, 4),
+            "packed_gbs": round(comp_bytes / (t * 1e-3) / 1e9, 1), "frac_of_hbm_peak": round(comp_bytes / (t * 1e-3) / 1e9 / peak, 4),
+            "note": "reads the packed stream once (algorithmic bytes = packed bytes), writes 8 B per block"}
+
+
+def run_reference_flow(torch, mc, d_in, seg, fields):
+    """One segment (positions, velocities, ids; 2^22 particles) through the host
+    library the way /root/reference/src/funcs.c drives a plugin: (a) literally,
+    quant_QField -> Register_GetCompressor -> CFunc -> checksum -> DFunc ->
+    quant_Field with one Compressor / Decompressor per field (src/funcs.c:13-76,
+    122-189; uint64 QFields cross the host boundary), (b) fused, MnwSeg_Encode /
+    MnwSeg_Decode. Wall clock, host arrays in and out."""
+    import ctypes as C
+    h = mc.host_lib()
+    pos = d_in[fields[0][0]:fields[0][0] + 3 * seg].cpu().numpy()
+    vel = d_in[fields[1][0]:fields[1][0] + 3 * seg].cpu().numpy()
+    ids = np.arange(seg, dtype=np.uint64)
+    pacc = mc.PositionAccuracy(None, POS_DELTA, BOX, 0)
+    vacc = mc.VelocityAccuracy(None, VEL_DELTA, 0, 0, 0.0)
+    iacc = mc.IDAccuracy(1024)
+    fl = (mc.Field * 3)()
+    fl[0] = mc.Field(mc.FieldHeader(FIELD_POSN, mc.ALGO_DIFF, mc.ALGO_VERSION, seg), 1, pos.ctypes.data, C.addressof(pacc))
+    fl[1] = mc.Field(mc.FieldHeader(FIELD_VELC, mc.ALGO_DIFF, mc.ALGO_VERSION, seg), 1, vel.ctypes.data, C.addressof(vacc))
+    fl[2] = mc.Field(mc.FieldHeader(mc.FIELD_PTID, mc.ALGO_DIFF, mc.ALGO_VERSION, seg), 1, ids.ctypes.data, C.addressof(iacc))
+    raw = pos.nbytes + vel.nbytes + ids.nbytes
+    cfunc = C.CFUNCTYPE(mc.CField, mc.QField, C.c_void_p)
+    dfunc = C.CFUNCTYPE(mc.QField, mc.CField, C.c_void_p)
+
+    def literal():
+        reg = h.Register_New()
+        cfs, ok = [], True
+        for i in range(3):
+            qf = h.quant_QField(fl[i])
+            comp = h.Register_GetCompressor(reg, mc.ALGO_DIFF, mc.ALGO_VERSION)
+            cf = cfunc(comp.CFunc)(qf, comp.Buffer)
+            cf.Checksum = h.MnwChecksum(cf.Data, cf.DataLen)
+            h.Register_FreeCompressor(reg, mc.ALGO_DIFF, mc.ALGO_VERSION, comp)
+            h.quant_FreeQField(qf)
+            cfs.append(cf)
+        for i in range(3):
+            dec = h.Register_GetDecompressor(reg, mc.ALGO_DIFF, mc.ALGO_VERSION)
+            qf = dfunc(dec.DFunc)(cfs[i], dec.Buffer)
+            f = h.quant_Field(qf)
+            if i == 2:
+                back = np.ctypeslib.as_array(C.cast(f.Data, C.POINTER(C.c_uint64)), shape=(seg,))
+                ok = bool(np.array_equal(back, ids))
+            h.Register_FreeDecompressor(reg, mc.ALGO_DIFF, mc.ALGO_VERSION, dec)
+            h.quant_FreeQField(qf)
+            h.quant_FreeField(f)
+            mc._libc.free(cfs[i].Data)
+        h.Register_Free(reg)
+        return ok
+
+    def fused():
+        cs = h.MnwSeg_Encode(mc.Seg(fl, 3))
+        s = h.MnwSeg_Decode(cs)
+        ok = all(s.Fields[i].Valid == 1 for i in range(3))
+        h.MnwSeg_Free(s)
+        h.MnwCSeg_Free(cs)
+        return ok
+
+    out = {"segment": "2^%d particles: positions, velocities, ids (%.0f MiB raw)" % (SEG_LOG2, raw / 2**20)}
+    for name, fn in (("literal", literal), ("fused", fused)):
+        ok = fn()
+        t0 = time.perf_counter()
+        reps = 3
+        for _ in range(reps):
+            ok = fn() and ok
+        el = (time.perf_counter() - t0) / reps
+        out[name] = {"ms": round(1e3 * el, 2), "gbs": round(2 * raw / el / 1e9, 3), "ok": bool(ok)}
+    out["note"] = ("encode + decode of one segment, wall clock; literal = uint64 QFields over the host boundary "
+                   "(8 B per value each way), one pooled context per field")
     return out
 
 

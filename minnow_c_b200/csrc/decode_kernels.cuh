@@ -25,6 +25,8 @@ struct DecodeParams {
     float *out;
     uint64_t *qOut;  // literal DFunc boundary: quantised values out, or null
     int *error;
+    uint32_t *dmgCount;  // tasks that hold a damaged block (k_damaged_tasks blanks those blocks afterwards)
+    uint32_t *dmgList;   // [nTasks]
 };
 
 constexpr int kJumpPows = 26;
@@ -300,17 +302,19 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
     uint4 ent = make_uint4(0u, 0u, 0u, 0u);
     float x0L = 0.0f;
     {
-        bool bad = false;
+        bool bad = false, damaged = false;
         if (lane < gCnt) {
             ent = __ldg(table + g0 + lane);
             const int gl = g0 + lane;
             const int compL = gl / fd.nb;
             const int lenL = min(kBlockLen, fd.n - (gl - compL * fd.nb) * kBlockLen);
-            // (a block whose checksum failed upstream is marked, not read: its values come out as NaN)
-            const bool damaged = ent.z == kWidthDamaged;
-            if (damaged) ent.z = 0u;
+            // A block whose checksum failed upstream is marked, not read: it goes through
+            // as a block of width 0 (its lanes draw their dither as usual, so the task's
+            // other blocks are untouched) and k_damaged_tasks blanks its values afterwards.
+            damaged = ent.z == kWidthDamaged;
+            if (damaged) ent.z = ent.w = 0u;
             const int size16L = (((lenL * (int)ent.z + 31) >> 5) + 3) >> 2;
-            bad = ent.z > (uint32_t)kMaxWidth || (!damaged && (int64_t)ent.w + size16L > payloadLen16);
+            bad = ent.z > (uint32_t)kMaxWidth || (int64_t)ent.w + size16L > payloadLen16;
             x0L = compL == 0 ? qp.X0[0] : compL == 1 ? qp.X0[1] : qp.X0[2];
             // Can util_Periodic move any value of this component? The values are
             // x0 + bw*q + dither with q up to the index of X1 (the component's own
@@ -321,12 +325,13 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
             float top = __fadd_rn(x1L, __fadd_rn(bw, bw));
             top = __fadd_rn(top, __fmul_rn(fabsf(top), 9.5367431640625e-07f));
             const bool inBox = x0L >= 0.0f && top < L;
-            ent.z |= (uint32_t)compL << 8 | (isPos && !inBox ? 1u << 10 : 0u) | (damaged ? 1u << 11 : 0u);
+            ent.z |= (uint32_t)compL << 8 | (isPos && !inBox ? 1u << 10 : 0u);
         }
         if (__any_sync(0xffffffffu, bad)) {
             if (lane == 0) atomicCAS(p.error, 0, kErrPayload);
             return;
         }
+        if (__any_sync(0xffffffffu, damaged) && lane == 0) p.dmgList[atomicAdd(p.dmgCount, 1u)] = (uint32_t)task;
     }
     const uint32_t rowAddr = (uint32_t)__cvta_generic_to_shared(st) + lane * 128 + ((lane & 7) << 4);
 
@@ -340,21 +345,6 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         const int b = g0 + k - comp * fd.nb;
         const int len = min(kBlockLen, fd.n - b * kBlockLen);
         const int size16 = (((len * w + 31) >> 5) + 3) >> 2;
-
-        if (zz & (1u << 11)) {
-            // damaged block: NaN (all ones at the DFunc boundary) for its values; the lane's
-            // stream still advances by its share, so the task's other blocks are untouched
-            const int mine = min(max(len - lane * kChunk, 0), kChunk);
-            if (kToQ) {
-                uint64_t *dstq = p.qOut + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
-                for (int el = lane; el < len; el += 32) dstq[el] = ~0ull;
-            } else {
-                for (int i = 0; i < mine; i++) (void)xs128p_next(s0, s1);
-                float *dstf = p.out + fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
-                for (int el = lane; el < len; el += 32) dstf[el] = __int_as_float(0x7fc00000);
-            }
-            continue;
-        }
 
         // ---- unpack ----
         const uint4 *src = payload + off16;
@@ -479,6 +469,44 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
         }
         __syncwarp();
     }
+}
+
+// ---------------------------------------------------------------------------
+// After k_unpack_dequant: the values of damaged blocks (segment image, a block
+// checksum failed) become NaN -- all ones at the DFunc boundary -- so that only
+// those particles are lost (doc/header_format/header_format.tex:188-196). One
+// CTA walks the (normally empty) list of tasks and resets it.
+// ---------------------------------------------------------------------------
+template <bool kToQ>
+__global__ void __launch_bounds__(128) k_damaged_tasks(DecodeParams p) {
+    const uint32_t n = *p.dmgCount;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t i = warp; i < n; i += 4) {
+        const int64_t task = p.dmgList[i];
+        int f;
+        if (p.uniformTasks > 0) {
+            f = (int)(task / p.uniformTasks);
+        } else {
+            const DevField *fields = p.fields;
+            f = find_field(p.nFields, task, [fields](int k) { return fields[k].firstTask; });
+        }
+        const DevField fd = p.fields[f];
+        const uint4 *table = reinterpret_cast<const uint4 *>(p.in + p.offsets[f] + 64);
+        const int g0 = (int)(task - fd.firstTask) * kRun;
+        const int gCnt = min(3 * fd.nb - g0, kRun);
+        for (int k = 0; k < gCnt; k++) {
+            if (__ldg(table + g0 + k).z != kWidthDamaged) continue;
+            const int comp = (g0 + k) / fd.nb, b = g0 + k - comp * fd.nb;
+            const int len = min(kBlockLen, fd.n - b * kBlockLen);
+            const int64_t at = fd.ioOff + (int64_t)comp * fd.n + (int64_t)b * kBlockLen;
+            for (int el = lane; el < len; el += 32) {
+                if (kToQ) p.qOut[at + el] = ~0ull;
+                else p.out[at + el] = __int_as_float(0x7fc00000);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *p.dmgCount = 0u;
 }
 
 }  // namespace mnw

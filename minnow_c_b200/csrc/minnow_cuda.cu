@@ -72,6 +72,7 @@ struct MnwCudaCtx {
     uint64_t ditherSeed = 0;
     Scratch fields, quant, minmax, tileState, seeds, tableOf, states, misc, ring;
     Scratch ioA, ioB, ioC, ioD;  // host-buffer entry points: device staging
+    Scratch dmg;                 // tasks holding a damaged block (k_damaged_tasks)
     Scratch jumpTab;        // columns of J^k for k < tabStreams (k_jump_table), built on first use
     int64_t tabStreams = 0;
     cudaEvent_t tabEv = nullptr;
@@ -214,7 +215,7 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
     cudaDeviceSynchronize();
     Scratch *all[] = {&ctx->fields, &ctx->quant, &ctx->minmax, &ctx->tileState, &ctx->seeds,
                       &ctx->tableOf, &ctx->states, &ctx->misc, &ctx->ring, &ctx->ioA, &ctx->ioB, &ctx->ioC,
-                      &ctx->ioD, &ctx->jumpTab};
+                      &ctx->ioD, &ctx->jumpTab, &ctx->dmg};
     for (Scratch *s : all) s->release();
     cudaFree(ctx->jumpPow);
     cudaFree(ctx->error);
@@ -577,9 +578,12 @@ extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, con
         }
         mark(ctx, 7, s);
         const unsigned dgrid = (unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps);
+        p.dmgCount = reinterpret_cast<uint32_t *>(ctx->error) + 32;  // zero between calls
+        p.dmgList = static_cast<uint32_t *>(ctx->dmg.need((size_t)pl.nTasks * 4));
         k_unpack_dequant<false><<<dgrid, kDecWarps * 32, 0, s>>>(p, pl.nTasks);
         mark(ctx, 8, s);
-        ctx->launches += 2;
+        k_damaged_tasks<false><<<1, 128, 0, s>>>(p);
+        ctx->launches += 3;
     }
     CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -140,9 +140,12 @@ uint64_t *decompress_dev(MnwCudaCtx *ctx, const CField &cf, MnwDiffHeader &h, in
     k_parse_headers<<<1, 128, 0, s>>>(p);
     ctx->launches++;
     if (pl.nTasks > 0) {
+        p.dmgCount = reinterpret_cast<uint32_t *>(ctx->error) + 32;
+        p.dmgList = static_cast<uint32_t *>(ctx->dmg.need((size_t)pl.nTasks * 4));
         k_unpack_dequant<true><<<(unsigned)((pl.nTasks + kDecWarps - 1) / kDecWarps), kDecWarps * 32, 0, s>>>(
             p, pl.nTasks);
-        ctx->launches++;
+        k_damaged_tasks<true><<<1, 128, 0, s>>>(p);
+        ctx->launches += 2;
     }
     CUDA_CHECK(cudaGetLastError());
     panic_on_status(ctx, s, who);
