@@ -312,14 +312,25 @@ def run_b200(args):
     d_dec = torch.empty_like(d_in)
     torch.cuda.synchronize()
 
+    # N > 1: the C multi-GPU driver (libminnow_nccl.so, include/minnow_nccl.h); only
+    # the ncclUniqueId travels through torch.distributed
+    shard = None
+    if world > 1:
+        uid = [mc.Sharded.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        shard = mc.Sharded(codec, rank, world, uid[0])
+        d_sizes = torch.zeros(world, dtype=torch.int64, device=dev)
+        d_base = torch.zeros(1, dtype=torch.int64, device=dev)
+
     def step(record=None):
         if record:
             record[0].record()
-        codec.encode_dev(d_in, descs, nf, d_out, d_off)
-        if world > 1:
-            # output placement of the sharded stream: all-gather of per-rank
-            # compressed sizes, exclusive prefix = this rank's base offset
-            _sizes, _base = sharded.exchange_sizes(d_off[nf:nf + 1])
+        if shard is not None:
+            # encode + output placement of the sharded stream in one C call: ncclAllGather
+            # of the per-rank packed sizes on the encode stream, exclusive prefix on the device
+            shard.encode(d_in, descs, nf, d_out, d_off, d_sizes, d_base)
+        else:
+            codec.encode_dev(d_in, descs, nf, d_out, d_off)
         if record:
             record[1].record()
         if args.encode_only:
@@ -386,7 +397,7 @@ def run_b200(args):
 
     gather = None
     if world > 1 and not args.no_gather:
-        gather = run_gather(torch, dist, sharded, d_out, d_off, nf, dev, rank)
+        gather = run_gather(torch, dist, shard, d_out, d_sizes, d_base, dev, rank)
     shard_parity = None
     if world > 1 and not args.no_cpu:
         shard_parity = sharded_parity(torch, dist, d_in, d_out, d_off, fields, dev, pick=(0, 1, nf - 2, nf - 1))
@@ -396,6 +407,8 @@ def run_b200(args):
     dec_gbs = n_gpus * raw_bytes * args.steps / (dec_ms * 1e-3) / 1e9
 
     if rank != 0:
+        if shard is not None:
+            shard.close()
         if world > 1:
             dist.destroy_process_group()
         return 0
@@ -468,40 +481,47 @@ def run_b200(args):
     if sweep is not None:
         line["sweep"] = sweep
     print(json.dumps(line), flush=True)
+    if shard is not None:
+        shard.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
-def run_gather(torch, dist, sharded, d_out, d_off, nf, dev, rank):
+def run_gather(torch, dist, shard, d_out, d_sizes, d_base, dev, rank):
     """Gather of the packed stream to rank 0 over NVLink (reported
-    on its own, it is not part of the encode/decode metric). Device-timed."""
-    sizes, _ = sharded.exchange_sizes(d_off[nf:nf + 1])
-    sizes_h = [int(v) for v in sizes.cpu()]
+    on its own, it is not part of the encode/decode metric): mnwnccl_GatherStream,
+    one grouped ncclSend/ncclRecv at the prefix offsets. Device-timed."""
+    sizes_h = [int(v) for v in d_sizes.cpu()]
     total = sum(sizes_h)
+    prefix_ok = int(d_base.item()) == sum(sizes_h[:rank])
     free = torch.cuda.mem_get_info(dev)[0]
-    if rank == 0 and total > free - (2 << 30):
-        ok = torch.zeros(1, device=dev)
-    else:
-        ok = torch.ones(1, device=dev)
+    ok = torch.tensor([0.0 if (rank == 0 and total > free - (2 << 30)) else 1.0], device=dev)
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     if float(ok.item()) == 0.0:
         return {"skipped": "sink has no room for the whole stream", "bytes": total}
-    local = d_out[:sizes_h[rank]]
-    sharded.gather_stream(local, sizes_h, dst=0)  # warm-up
+    d_global = torch.empty(total, dtype=torch.uint8, device=dev) if rank == 0 else None
+    shard.gather(d_out, sizes_h, 0, d_global)  # warm-up
     torch.cuda.synchronize()
     dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    out = sharded.gather_stream(local, sizes_h, dst=0)
+    shard.gather(d_out, sizes_h, 0, d_global)
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    del out
+    # the sink's copy of this rank's slab must be the slab (checked on rank 0 for its own, cheaply)
+    same = True
+    if rank == 0:
+        same = bool(torch.equal(d_global[:sizes_h[0]], d_out[:sizes_h[0]]))
+    del d_global
     moved = total - sizes_h[0]
-    return {"ms": float(ms.item()), "bytes_into_sink": moved, "gbs": moved / (float(ms.item()) * 1e-3) / 1e9,
-            "note": "ncclSend/Recv of each rank's packed slab to rank 0; not part of the metric"}
+    gbs = moved / (float(ms.item()) * 1e-3) / 1e9
+    return {"ms": float(ms.item()), "bytes_into_sink": moved, "gbs": gbs, "frac_of_900_gbs_ingress": gbs / 900.0,
+            "prefix_ok": bool(prefix_ok), "sink_slab_ok": same,
+            "note": "mnwnccl_GatherStream: one ncclGroupStart..ncclSend/ncclRecv x ranks..ncclGroupEnd into rank 0; "
+                    "not part of the metric"}
 
 
 def roundtrip_check(torch, d_in, d_dec, fields, seg):

@@ -102,6 +102,9 @@ void mnwcuda_Destroy(MnwCudaCtx *ctx);
  *   decode: DFunc (src/funcs.c:54) followed by quant_Field
  *           (src/quant.c:146-155 -> undoPosition()/undoVelocity() :451-551:
  *           util_UndoUniformBinIndex, util_Periodic).
+ * Input floats must be finite: the reference's own arithmetic is undefined for
+ * NaN / infinity (the float -> uint32 cast of src/util.c:190) and nothing here
+ * detects them.
  * d_in/d_out/d_offsets are device pointers; h_fields is a host array.
  * Field f's payload is d_out[d_offsets[f] .. d_offsets[f+1]); d_offsets has
  * nFields+1 entries. `stream` is a cudaStream_t (NULL = default stream).

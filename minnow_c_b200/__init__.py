@@ -20,6 +20,7 @@ ROOT = os.path.dirname(_HERE)
 # (MNWCUDA_LIB: kernel experiments load a differently built library of the same ABI)
 LIB_PATH = os.environ.get("MNWCUDA_LIB") or os.path.join(_HERE, "libminnow_cuda.so")
 HOST_LIB_PATH = os.path.join(_HERE, "libminnow_host.so")
+NCCL_LIB_PATH = os.path.join(_HERE, "libminnow_nccl.so")
 
 FIELD_POSN = 0x506F736E
 FIELD_VELC = 0x56656C63
@@ -50,6 +51,18 @@ def build(verbose=False):
         cmd.insert(1, "-Xptxas=-v")
     subprocess.check_call(cmd)
     return LIB_PATH
+
+
+def build_nccl():
+    """Compile libminnow_nccl.so (the C multi-GPU driver; links libminnow_cuda and NCCL)."""
+    src = os.path.join(_HERE, "csrc", "minnow_nccl.cu")
+    deps = [src, os.path.join(ROOT, "include", "minnow_nccl.h"), os.path.join(ROOT, "include", "minnow_cuda.h")]
+    if os.path.exists(NCCL_LIB_PATH) and all(os.path.getmtime(NCCL_LIB_PATH) >= os.path.getmtime(d) for d in deps):
+        return NCCL_LIB_PATH
+    subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
+                           "-shared", "-Xcompiler", "-fPIC", "-I" + os.path.join(ROOT, "include"), "-o", NCCL_LIB_PATH,
+                           src, "-L" + _HERE, "-lminnow_cuda", "-lnccl", "-Xlinker", "-rpath=$ORIGIN"])
+    return NCCL_LIB_PATH
 
 
 # ---- ctypes images of the boundary structs (include/minnow_types.h) ----
@@ -221,8 +234,23 @@ HOST_EXPORTS = {
     "MnwQuant_SetDitherSeed": (None, [C.c_uint64]),
 }
 
+NCCL_EXPORTS = {
+    "mnwnccl_UniqueId": (C.c_int, [C.c_void_p]),
+    "mnwnccl_Init": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "mnwnccl_Finalize": (None, [C.c_void_p]),
+    "mnwnccl_Rank": (C.c_int, [C.c_void_p]),
+    "mnwnccl_World": (C.c_int, [C.c_void_p]),
+    "mnwnccl_EncodeSharded": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64, C.c_void_p, C.c_int64,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mnwnccl_DecodeSharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(FieldDesc), C.c_int64, C.c_void_p,
+                                        C.c_void_p]),
+    "mnwnccl_GatherStream": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "mnwnccl_ScatterStream": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+}
+
 _lib = None
 _host = None
+_nccl = None
 _libc = C.CDLL(None)
 _libc.free.argtypes = [C.c_void_p]
 
@@ -257,6 +285,74 @@ def host_lib():
             fn.argtypes = args
         _host = handle
     return _host
+
+
+def nccl_lib():
+    """The loaded libminnow_nccl.so (C multi-GPU driver). torch is imported first so that
+    its bundled libnccl.so.2 is the one both share."""
+    global _nccl
+    if _nccl is None:
+        import torch  # noqa: F401
+        lib()
+        if not os.path.exists(NCCL_LIB_PATH):
+            raise RuntimeError("libminnow_nccl.so is not built (run __graft_entry__.build())")
+        handle = C.CDLL(NCCL_LIB_PATH)
+        for name, (res, args) in NCCL_EXPORTS.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _nccl = handle
+    return _nccl
+
+
+class Sharded:
+    """One rank of the C multi-GPU driver (include/minnow_nccl.h) over a Codec."""
+
+    def __init__(self, codec, rank, world, unique_id):
+        self.codec, self.rank, self.world = codec, rank, world
+        buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+        self.h = nccl_lib().mnwnccl_Init(codec.ctx, rank, world, buf)
+        if not self.h:
+            raise RuntimeError("mnwnccl_Init failed")
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * 128)()
+        if nccl_lib().mnwnccl_UniqueId(buf):
+            raise RuntimeError("mnwnccl_UniqueId failed")
+        return bytes(buf)
+
+    def close(self):
+        if self.h:
+            nccl_lib().mnwnccl_Finalize(self.h)
+            self.h = None
+
+    def encode(self, d_in, descs, n_fields, d_out, d_offsets, d_sizes, d_base, stream=None):
+        rc = nccl_lib().mnwnccl_EncodeSharded(self.h, d_in.data_ptr(), descs, n_fields, d_out.data_ptr(),
+                                              d_out.numel() * d_out.element_size(), d_offsets.data_ptr(),
+                                              d_sizes.data_ptr(), d_base.data_ptr(), _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwnccl_EncodeSharded: %d" % rc)
+
+    def decode(self, d_in, d_offsets, descs, n_fields, d_out, stream=None):
+        rc = nccl_lib().mnwnccl_DecodeSharded(self.h, d_in.data_ptr(), d_offsets.data_ptr(), descs, n_fields,
+                                              d_out.data_ptr(), _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwnccl_DecodeSharded: %d" % rc)
+
+    def gather(self, d_local, sizes, root, d_global=None, stream=None):
+        arr = (C.c_uint64 * self.world)(*[int(v) for v in sizes])
+        rc = nccl_lib().mnwnccl_GatherStream(self.h, d_local.data_ptr(), arr, root,
+                                             d_global.data_ptr() if d_global is not None else None, _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwnccl_GatherStream: %d" % rc)
+
+    def scatter(self, d_global, sizes, root, d_local, stream=None):
+        arr = (C.c_uint64 * self.world)(*[int(v) for v in sizes])
+        rc = nccl_lib().mnwnccl_ScatterStream(self.h, d_global.data_ptr() if d_global is not None else None, arr, root,
+                                              d_local.data_ptr(), _stream_ptr(stream))
+        if rc:
+            raise ValueError("mnwnccl_ScatterStream: %d" % rc)
 
 
 def field_bound(n):

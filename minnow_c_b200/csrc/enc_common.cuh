@@ -61,13 +61,6 @@ constexpr uint32_t kQBias = 0x4b000000u;  // bit pattern of 2^23: trunc by add.r
 
 enum : int { kWorkNop = 0, kWorkA = 1, kWorkB = 2, kWorkStop = 3 };
 
-struct BlockRec {  // what placement needs to know about a parked block
-    uint32_t first;
-    int32_t minDelta;
-    uint32_t width;
-    uint32_t size16;
-};
-
 struct EncodeParams {
     const float *in;
     const uint64_t *qIn;   // literal CFunc boundary: quantised values in, or null
@@ -98,31 +91,15 @@ struct EncodeParams {
 };
 
 // ---- memory-ordering helpers ----
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_u32(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p) {
     uint32_t v;
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint64_t ld_acquire_u64(const uint64_t *p) {
-    uint64_t v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *p) {
     uint64_t v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
-}
-__device__ __forceinline__ void st_release_u64(uint64_t *p, uint64_t v) {
-    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ uint4 ld_relaxed_u4(const void *p) {
     uint4 v;

@@ -57,13 +57,20 @@ __device__ __forceinline__ float unwrap_t(float v, const Unwrap &u) {
     return r;
 }
 
-// util_UniformBinIndex (src/util.c:184-191) on 32 values per lane. See
-// bin_index_fast (minnow_kernels.cuh) for the division-free scaling. With
+// util_UniformBinIndex (src/util.c:184-191) on 32 values per lane, without the
+// IEEE division: t = RN_f(a/dx) with a = x - x0, q = t<0 ? 0 : t>=1 ? top :
+// trunc(t * 2^depth). Multiplying by 2^depth is exact, so q = trunc(RN_f(a *
+// 2^depth/dx)) outside the subnormal range (where q = 0 on both sides). The
+// quotient of two 24-bit floats is never closer than 2^-49 (relative) to a
+// rounding midpoint of the 24-bit format, and RN_d(a * RN_d(2^depth/dx)) is within
+// 2^-52 of the true scaled quotient, so rounding that double to float gives exactly
+// RN_f(a/dx) * 2^depth (DESIGN.md section 5 has the proof). With
 // kBiased (depth <= 23) the truncation is an add in round-toward-zero mode:
 // for 0 <= s < 2^23, RZ(s + 2^23) = 2^23 + floor(s) exactly, i.e. the result's
 // bit pattern is kQBias + q; the bias cancels in the deltas. The clamp t >= 1
 // becomes fmin against the largest index (an integer, so trunc commutes).
 // s >= 0 always: x0 is the minimum of the very same unwrapped values.
+
 // the lane's 32 consecutive values of a staged block (128-byte swizzle), as bit patterns
 __device__ __forceinline__ void load_block32(const float *stage, int lane, uint32_t (&q)[kChunk]) {
 #pragma unroll

@@ -324,9 +324,9 @@ constexpr int64_t kTabMaxStreams = 1 << 16;  // above: the table would exceed 12
 
 struct Plan {
     std::vector<DevField> fields;
-    int64_t nTiles = 0, nBlocks = 0, nTasks = 0, fixedTotal = 0, maxStreams = 0;
-    int uniformTiles = 0, uniformBlocks = 0, uniformTasks = 0;
-    int64_t maxTilesPerField = 0, maxBlocksPerField = 0;
+    int64_t nBlocks = 0, nTasks = 0, fixedTotal = 0, maxStreams = 0;
+    int uniformBlocks = 0, uniformTasks = 0;
+    int64_t maxBlocksPerField = 0;
     int64_t floatEnd = 0;  // one past the last input float any field refers to
     bool hasEmpty = false;
 };
@@ -344,29 +344,24 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
         f.ioOff = d.Offset;
         f.fixedBase = pl.fixedTotal;
         f.firstBlock = pl.nBlocks;
-        f.firstTile = pl.nTiles;
         f.firstTask = pl.nTasks;
         f.n = d.ParticleLen;
         f.nb = (int32_t)nblocks_of(d.ParticleLen);
         f.fieldCode = d.FieldCode;
         f.delta = d.Delta;
         f.width = d.Width;
-        f.tilesPerComp = (f.nb + kTileBlocks - 1) / kTileBlocks;
         f.seed = d.DitherSeed;
         int64_t tasks = (3 * (int64_t)f.nb + kRun - 1) / kRun;
         pl.fixedTotal += mnwcuda_FieldFixedBytes(d.ParticleLen);
         pl.nBlocks += 3 * (int64_t)f.nb;
-        pl.nTiles += 3 * (int64_t)f.tilesPerComp;
         pl.nTasks += tasks;
         if (tasks * 32 > pl.maxStreams) pl.maxStreams = tasks * 32;
         if (3 * (int64_t)f.nb > pl.maxBlocksPerField) pl.maxBlocksPerField = 3 * (int64_t)f.nb;
-        if (3 * (int64_t)f.tilesPerComp > pl.maxTilesPerField) pl.maxTilesPerField = 3 * (int64_t)f.tilesPerComp;
         if (d.Offset + 3ll * d.ParticleLen > pl.floatEnd) pl.floatEnd = d.Offset + 3ll * d.ParticleLen;
         if (d.ParticleLen == 0) pl.hasEmpty = true;
         if (d.ParticleLen != h[0].ParticleLen || d.ParticleLen == 0) uniform = false;
     }
     if (uniform && nFields > 0) {
-        pl.uniformTiles = 3 * pl.fields[0].tilesPerComp;
         pl.uniformBlocks = 3 * pl.fields[0].nb;
         pl.uniformTasks = (int)((3 * (int64_t)pl.fields[0].nb + kRun - 1) / kRun);
     }

@@ -11,9 +11,6 @@ namespace mnw {
 
 constexpr int kBlockLen = MNWCUDA_BLOCK_LEN;   // values per pack block (one warp)
 constexpr int kChunk = 32;                     // consecutive values per lane
-constexpr int kWarpsPerCta = 8;                // encode: one block per warp
-constexpr int kTileBlocks = kWarpsPerCta;      // blocks per encode tile
-constexpr int kTileVals = kTileBlocks * kBlockLen;
 constexpr int kRun = MNWCUDA_DITHER_RUN;       // blocks per decode task
 constexpr int kMaxWidth = 25;                  // residual bits: |delta| < 2^24
 constexpr int kStageWords = 1024 + 32;         // per-warp staging: 1024 words + skew pads
@@ -25,14 +22,12 @@ struct DevField {
     int64_t ioOff;       // first float of the field in the float buffer
     int64_t fixedBase;   // sum of fixed bytes (header+table) of earlier fields
     int64_t firstBlock;  // sum of 3*nb of earlier fields
-    int64_t firstTile;   // encode tiles of earlier fields
     int64_t firstTask;   // decode tasks of earlier fields
     int32_t n;           // particles
     int32_t nb;          // blocks per component
     uint32_t fieldCode;
     float delta;
     float width;
-    int32_t tilesPerComp;
     uint64_t seed;
 };
 
@@ -43,16 +38,7 @@ struct DevQuant {
     float maxDiff;
     uint32_t depth;
     float width;   // decode: box width from the payload header (Posn)
-    double scale;  // encode: RN_double(2^depth / maxDiff), see bin_index_fast
-};
-
-// Per-block result of the pack kernel before the table is finalised.
-struct TmpBlock {
-    uint32_t first;
-    int32_t minDelta;
-    uint32_t width;
-    uint32_t size16;    // packed size, 16-byte units
-    uint64_t prefix16;  // payload offset over the whole batch, 16-byte units
+    double scale;  // encode: RN_double(2^depth / maxDiff), see quantise32 (enc_math.cuh)
 };
 
 // ---- order-preserving float <-> uint32 (for atomicMin/atomicMax) ----
@@ -63,25 +49,6 @@ __device__ __forceinline__ uint32_t ord_from_float(float v) {
 __device__ __forceinline__ float float_from_ord(uint32_t o) {
     uint32_t b = o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu);
     return __uint_as_float(b);
-}
-
-// util_UndoPeriodic's per-element rule (src/util.c:106-110), branch-free:
-// sub, two compares (the second masked by the first, as in the reference's
-// else-if), two predicated adds
-__device__ __forceinline__ float unwrap(float v, float anchor, float L, float half) {
-    float r = v;
-    asm("{\n\t"
-        ".reg .pred up, dn;\n\t"
-        ".reg .f32 rel, nh;\n\t"
-        "sub.rn.f32 rel, %1, %2;\n\t"
-        "neg.f32 nh, %4;\n\t"
-        "setp.ge.f32 up, rel, %4;\n\t"
-        "setp.lt.and.f32 dn, rel, nh, !up;\n\t"
-        "@up sub.rn.f32 %0, %1, %3;\n\t"
-        "@dn add.rn.f32 %0, %1, %3;\n\t"
-        "}"
-        : "+f"(r) : "f"(v), "f"(anchor), "f"(L), "f"(half));
-    return r;
 }
 
 // util_Periodic's per-element rule (src/util.c:76-82)
@@ -96,32 +63,6 @@ __device__ __forceinline__ float wrap(float v, float L) {
         "}"
         : "+f"(r) : "f"(v), "f"(L));
     return r;
-}
-
-// util_UniformBinIndex's per-element rule (src/util.c:184-191): IEEE division,
-// clamp, scale, truncate. No contraction anywhere.
-__device__ __forceinline__ uint32_t bin_index(float v, float x0, float dx, float bins,
-                                              uint32_t top) {
-    float t = __fdiv_rn(__fsub_rn(v, x0), dx);
-    if (t < 0.0f) return 0u;
-    if (t >= 1.0f) return top;
-    return __float2uint_rz(__fmul_rn(t, bins));
-}
-
-// The same index without the IEEE float division. util.c:184-191 computes
-//   t = RN_f(a/dx);  q = t<0 ? 0 : t>=1 ? top : trunc(t * 2^depth)
-// with a = x-x0. Multiplying by 2^depth is exact, so q = trunc(RN_f(a/dx)*2^depth)
-// = trunc(RN_f(a * 2^depth/dx)) outside the subnormal range (where q = 0 on both
-// sides). The quotient of two 24-bit floats is never closer than 2^-49
-// (relative) to a rounding midpoint of the 24-bit format, and
-// RN_d(a * RN_d(2^depth/dx)) is within 2^-52 of the true scaled quotient, so
-// rounding that double to float gives exactly RN_f(a/dx)*2^depth. cvt.rzi.u32
-// saturates negatives (t<0) and NaN (0/0 on a constant field) to 0, and the
-// t>=1 clamp becomes an integer min. DESIGN.md "quantiser" has the proof.
-__device__ __forceinline__ uint32_t bin_index_fast(float v, float x0, double scale, uint32_t top) {
-    float a = __fsub_rn(v, x0);
-    float s = __double2float_rn(__dmul_rn((double)a, scale));
-    return min(__float2uint_rz(s), top);
 }
 
 // xorshift128+ (55,14,36), src/rand.c:80-90; returns s0+s1 of the old state
@@ -193,21 +134,6 @@ __device__ __forceinline__ int find_field(int nFields, int64_t idx, GetFirst fir
         if (first(mid) <= idx) lo = mid; else hi = mid - 1;
     }
     return lo;
-}
-
-__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t *p) {
-    uint64_t v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ void st_volatile_u64(uint64_t *p, uint64_t v) {
-    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ float4 ld_stream_f4(const float4 *p) {
-    float4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
-    return r;
 }
 
 __device__ __forceinline__ uint4 ld_stream_u4(const uint4 *p) {

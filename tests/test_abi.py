@@ -49,3 +49,17 @@ def test_struct_layouts():
     assert C.sizeof(mc.FieldDesc) == 32
     import _oracle
     assert _oracle.HEADER_DTYPE.itemsize == 64 and _oracle.ENTRY_DTYPE.itemsize == 16
+
+
+def test_nccl_driver_exports_every_declared_symbol():
+    """libminnow_nccl.so (include/minnow_nccl.h): symbols only -- loading it needs libnccl, which this image has"""
+    mc.build()
+    path = mc.build_nccl()
+    text = open(os.path.join(mc.ROOT, "include", "minnow_nccl.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = sorted(set(re.findall(r"\b(mnwnccl_\w+)\s*\(", text)))
+    assert set(names) == set(mc.NCCL_EXPORTS)
+    import subprocess
+    syms = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True).stdout
+    for name in names:
+        assert (" T " + name) in syms, name

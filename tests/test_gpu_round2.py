@@ -261,3 +261,35 @@ def test_two_contexts_encode_concurrently():
     finally:
         ca.close()
         cb.close()
+
+
+def test_c_nccl_driver_world_of_one(codec):
+    """libminnow_nccl.so through its C ABI with a communicator of one rank: the
+    sharded encode is the plain encode, sizes[0] = the packed bytes, base = 0,
+    gather and scatter move the slab. (N >= 2 runs through bench.py --gpus N.)"""
+    d_in, fields = _slab(codec, 2, 1 << 16, 128, 900)
+    want, offs_want = _encode(codec, d_in, fields)
+    nf = len(fields)
+    sh = mc.Sharded(codec, 0, 1, mc.Sharded.unique_id())
+    try:
+        d_out = torch.zeros(sum(mc.field_bound(f[1]) for f in fields), dtype=torch.uint8, device="cuda")
+        d_off = torch.zeros(nf + 1, dtype=torch.int64, device="cuda")
+        d_sizes = torch.full((1,), -1, dtype=torch.int64, device="cuda")
+        d_base = torch.full((1,), -1, dtype=torch.int64, device="cuda")
+        sh.encode(d_in, mc.make_descs(fields), nf, d_out, d_off, d_sizes, d_base)
+        assert codec.status() == 0
+        assert int(d_sizes[0]) == want.size and int(d_base[0]) == 0
+        assert np.array_equal(d_off.cpu().numpy(), offs_want)
+        d_glob = torch.zeros(want.size, dtype=torch.uint8, device="cuda")
+        sh.gather(d_out, [want.size], 0, d_glob)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_glob.cpu().numpy(), want)
+        d_loc = torch.zeros(want.size, dtype=torch.uint8, device="cuda")
+        sh.scatter(d_glob, [want.size], 0, d_loc)
+        d_dec = torch.zeros_like(d_in)
+        sh.decode(d_loc, d_off, mc.make_descs(fields), nf, d_dec)
+        assert codec.status() == 0
+        err = (d_dec - d_in).abs()
+        assert float(err[3 * (1 << 16):].max()) <= 1.0 + 1e-3  # velocities of segment 0: Delta = 1
+    finally:
+        sh.close()
