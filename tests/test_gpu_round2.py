@@ -290,6 +290,6 @@ def test_c_nccl_driver_world_of_one(codec):
         sh.decode(d_loc, d_off, mc.make_descs(fields), nf, d_dec)
         assert codec.status() == 0
         err = (d_dec - d_in).abs()
-        assert float(err[3 * (1 << 16):].max()) <= 1.0 + 1e-3  # velocities of segment 0: Delta = 1
+        assert float(err[3 * (1 << 16):6 * (1 << 16)].max()) <= 1.0 + 1e-3  # velocities of segment 0: Delta = 1
     finally:
         sh.close()
