@@ -27,7 +27,9 @@ constexpr unsigned kFull = 0xffffffffu;
 #define MNW_ENC_CONSUMERS 18
 #endif
 constexpr int kEncConsumers = MNW_ENC_CONSUMERS;
-constexpr int kEncWarps = kEncConsumers + 2;  // per CTA (one CTA per SM): producer, consumers, a service warp (scan in CTA 0, reduce in CTA 1)
+constexpr int kEncWarps = kEncConsumers + 2;  // per CTA (one CTA per SM): planner, issuer, consumers; the last warp of CTA 0 is the scan
+                                              // warp, of CTA 1 the reduce warp (elsewhere it is a consumer like the others)
+constexpr int kDescQ = 96;           // descriptor queue: the planner runs up to kDescQ - kEncStages slots ahead of the issuer
 constexpr int kEncStageBytes = 4096;
 constexpr int kGroupSlots = 32;      // slots per ticket
 constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
@@ -37,18 +39,22 @@ constexpr int kArenaWords = 832;     // per consumer: packed blocks waiting for 
 // input ring: 4 KiB blocks (TMA, 128-byte swizzle), as many stages as the SM's shared memory holds
 // next to the consumers' arenas and records
 constexpr int kEncPerConsumer = kFifo * (16 + 8 + 8) + 64 + kArenaWords * 4;
-constexpr int kEncStages = (232448 - 32 - kEncConsumers * kEncPerConsumer) / (kEncStageBytes + 2 * 8 + 80 + 4);
+constexpr int kEncTimelineBytes = 1024;  // MNWCUDA_ENCODE_STATS: issue / hand-back clocks of up to 64 stages
+constexpr int kEncStages = (232448 - 32 - kEncTimelineBytes - kDescQ * 80 - kEncConsumers * kEncPerConsumer) / (kEncStageBytes + 2 * 8 + 4);
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
-constexpr int kEncCtrlBytes = (2 * kEncStages * 8 + kEncStages * 80 + 16 + kEncStages * 4 + 15) & ~15;
+constexpr int kEncCtrlBytes = (2 * kEncStages * 8 + kDescQ * 80 + 16 + kEncStages * 4 + 15) & ~15;
 constexpr int kEncFifoOff = kEncCtrlOff + kEncCtrlBytes;   // per consumer: records of its parked blocks
 constexpr int kEncFifoBytes = kEncConsumers * kFifo * (16 + 8 + 8);
 constexpr int kEncStatOff = kEncFifoOff + kEncFifoBytes;   // per consumer: 8 phase clocks (MNWCUDA_ENCODE_STATS)
 constexpr int kEncArenaOff = kEncStatOff + kEncConsumers * 64;
-constexpr int kEncSmemBytes = kEncArenaOff + kEncConsumers * kArenaWords * 4;
+constexpr int kEncTimelineOff = kEncArenaOff + kEncConsumers * kArenaWords * 4;
+constexpr int kEncSmemBytes = kEncTimelineOff + kEncTimelineBytes;
+static_assert(kEncStages <= 64, "k_encode: the stage timeline holds 64 stages");
 static_assert(kEncSmemBytes <= 232448, "k_encode: more shared memory than an SM has");
 static_assert(kArenaWords >= 33 * 25 + 1, "k_encode: the arena must hold one block of any width");
 static_assert(kEncStages >= 16, "k_encode: too few ring stages");
+static_assert(kDescQ >= kEncStages + kGroupSlots, "k_encode: the descriptor queue must hold a pass beyond the ring");
 constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bits x 1024, 16-byte padded
 
 constexpr uint32_t kAggReady = 0x8000u;       // in a 16-bit size word
@@ -76,6 +82,7 @@ struct EncodeParams {
     uint4 *tbl;            // [nBlocks] First, MinDelta, Width of the block (k_tables adds Offset16)
     uint64_t *blkMM;       // [nBlocks, padded to kRedWin] ord(min) | ~ord(max) << 32 of the block, 0 = not there yet
     uint64_t *fq;          // [nFields][3][2] published parameters of a component (see publish_quant)
+    uint64_t *winMM;       // [nBlocks / kRedWin] the same per reduce window (parallel reduce), 0 = not there yet
     uint32_t *scratch;     // [CTAs][kEncConsumers][kFifo][kSlotWords] packed blocks waiting for their offset
     int64_t tmaShift;      // floats between the tensor map's 128-byte aligned base and `in`; <0: no TMA
     int64_t tmaRows;       // rows of 32 floats covered by the tensor map

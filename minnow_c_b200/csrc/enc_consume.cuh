@@ -9,6 +9,7 @@ namespace mnw {
 __device__ __forceinline__ void release_stage(const RingCtrl &rc, int s, bool wrote, int lane) {
     __syncwarp();
     if (lane == 0) {
+        if (rc.tRel) rc.tRel[s] = clock64();  // (statistics build only)
         if (wrote) fence_proxy_async();  // generic-proxy writes before the TMA's next fill
         rc.uses[s] = rc.uses[s] + 1;     // one owner at a time
         mbar_arrive(rc.empty + s);
@@ -255,7 +256,11 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
     uint32_t *tmp = ff.arena + loc;
     __syncwarp();
     MNW_PHASE(2)
+#if defined(MNW_ABLATE) && (MNW_ABLATE & 2)
+    if (bs.w > 0 && lane == 0) tmp[0] = q[0] + q[31];  // timing experiment only: no packing
+#else
     if (bs.w > 0) pack_dispatch(bs.w, q, tmp, lane);
+#endif
     MNW_PHASE(3)
     const int k = (ff.head + ff.count) % kFifo;
     if (lane == 0) {

@@ -6,7 +6,7 @@
 namespace mnw {
 
 // ---------------------------------------------------------------------------
-// k_encode: warp 0 = producer, warps 1..18 = consumers, warp 19 = the scan warp
+// k_encode: warp 0 = planner, warp 1 = issuer, then the consumers, the last warp = the scan warp
 // in CTA 0 and the reduce warp in CTA 1 (the host launches at least two CTAs).
 // ---------------------------------------------------------------------------
 // kStats: the per-phase clocks of MNWCUDA_ENCODE_STATS; a separate instantiation so
@@ -17,13 +17,18 @@ __global__ void __launch_bounds__(kEncWarps * 32, 1)
 k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) uint8_t encSmem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const RingCtrl rc = ring_ctrl(encSmem);
+    RingCtrl rc = ring_ctrl(encSmem);
+    if (kStats && p.stats) {
+        rc.tIssue = reinterpret_cast<long long *>(encSmem + kEncTimelineOff);
+        rc.tRel = rc.tIssue + 64;
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < kEncStages; s++) {
             mbar_init(rc.full + s, 1);
             mbar_init(rc.empty + s, 1);
         }
-        *rc.qHead = 0;
+        rc.qHead[0] = rc.qHead[1] = rc.qHead[2] = 0;  // claimed, planned, issued
+        rc.qHead[3] = 0xffffffffu;                    // end of the sequence: not known yet
         for (int s = 0; s < kEncStages; s++) rc.uses[s] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_proxy_async();
@@ -32,17 +37,31 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     // with enough CTAs the first two do nothing but scan and reduce: a service warp that
     // shares its SM with 18 busy consumers falls behind, and everybody waits for it
     const bool service = gridDim.x >= 8 && blockIdx.x < 2;
-    if (service && warp != kEncWarps - 1) return;
+    if (service && warp != kEncWarps - 1) {
+        // CTA 1 of a big launch: its other warps reduce the windows in parallel
+        if (blockIdx.x == 1 && warp < kRedWarps && p.lagG >= 0 && !kFromQ && reduce_in_parallel(p))
+            reduce_windows(p, lane, warp);
+        return;
+    }
+    // the last warp: scan in CTA 0, reduce in CTA 1, one more consumer everywhere else
+    const bool lastIsService = blockIdx.x < 2;
     if (warp == 0) {
-        producer<kFromQ>(p, &tmap, encSmem, rc, lane);
+        planner<kFromQ, kStats>(p, &tmap, rc, lane, lastIsService ? kEncConsumers - 1 : kEncConsumers);
         return;
     }
-    if (warp == kEncWarps - 1) {
+    if (warp == 1) {
+        issuer<kStats>(p, &tmap, encSmem, rc, lane);
+        return;
+    }
+    if (warp == kEncWarps - 1 && lastIsService) {
         if (blockIdx.x == 0) scan_blocks(p, lane);
-        else if (blockIdx.x == 1 && p.lagG >= 0 && !kFromQ) reduce_fields(p, lane);
+        else if (p.lagG >= 0 && !kFromQ) {
+            if (gridDim.x >= 8 && reduce_in_parallel(p)) reduce_fold(p, lane);
+            else reduce_fields(p, lane);
+        }
         return;
     }
-    const int c = warp - 1;
+    const int c = warp - 2;
     ParkFifo ff;
     ff.where = reinterpret_cast<int4 *>(encSmem + kEncFifoOff) + c * kFifo;
     ff.blk = reinterpret_cast<int64_t *>(encSmem + kEncFifoOff + kEncConsumers * kFifo * 16) + c * kFifo;
@@ -59,7 +78,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         __syncwarp();
     }
     bool drain = false;
-    long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0;
+    long long tA = 0, tB = 0, tQueue = 0, nA = 0, nB = 0, tFill = 0, nFill = 0;
     const long long tStart = kStats ? clock64() : 0;
     while (true) {
         const long long c0 = kStats ? clock64() : 0;
@@ -79,10 +98,14 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             if (spin_expired(clk)) { spin_timeout(p.error, 7, -1); return; }
         }
         if (!mbar_wait(p.error, rc.full + s, use & 1u, 5)) return;
-        WorkDesc d = rc.desc[s];
+        WorkDesc d = rc.desc[seq % kDescQ];
         float *stage = reinterpret_cast<float *>(encSmem + kEncRingOff + s * kEncStageBytes);
         const long long c1 = kStats ? clock64() : 0;
         if (kStats) {
+            if (rc.tIssue && d.kind != kWorkStop) {  // stage timeline: fill -> data seen by its consumer
+                tFill += c1 - rc.tIssue[s];
+                nFill++;
+            }
             tQueue += c1 - c0;
             if (ff.wst && lane == 0 && d.kind == kWorkA) ff.wst[6] += c1 - c0;  // stats: the part spent waiting for A blocks
         }
@@ -121,6 +144,8 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         atomicAdd(p.stats + 6, (unsigned long long)nB);
         atomicAdd(p.stats + 7, (unsigned long long)(clock64() - tStart));
         for (int i = 0; i < 8; i++) atomicAdd(p.stats + 8 + i, ff.wst[i]);
+        atomicAdd(p.stats + 16, (unsigned long long)tFill);
+        atomicAdd(p.stats + 17, (unsigned long long)nFill);
     }
 }
 

@@ -121,7 +121,13 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
             bool all = true;
 #pragma unroll
             for (int j = 0; j < 4; j++) all = all && agg_ready(cur[j]);
-            if (__all_sync(kFull, all)) break;
+            if (__all_sync(kFull, all)) {
+                if (p.stats && lane == 0) {  // MNWCUDA_ENCODE_STATS: was the window complete at first look?
+                    p.stats[25] += 1;
+                    p.stats[26] += clk.spins == 0;
+                }
+                break;
+            }
             if (spin_expired(clk)) {
                 if (lane == 0) spin_timeout(p.error, 3, base);
                 return;
@@ -245,7 +251,13 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
                           (b0 + 1 >= winEnd || (cur[j].z | cur[j].w) != 0u);
                 }
             }
-            if (__all_sync(kFull, all)) break;
+            if (__all_sync(kFull, all)) {
+                if (p.stats && lane == 0) {
+                    p.stats[27] += 1;
+                    p.stats[28] += clk.spins == 0;
+                }
+                break;
+            }
             if (spin_expired(clk)) {
                 if (lane == 0) spin_timeout(p.error, 6, base);
                 return;
@@ -298,6 +310,92 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
 }
 
 // ---------------------------------------------------------------------------
+// The same in parallel, for batches whose components are whole numbers of reduce
+// windows (every bench-sized batch): one window is one L2 round trip for a warp, and
+// a single warp walking the windows in order gets through exactly one per round trip
+// -- measured, it never waited for the A work: everybody waited for it. So kRedWarps
+// warps of CTA 1 take the windows round robin and publish one word per window
+// (ord(min) | ~ord(max) << 32, never zero), and one more warp folds those words in
+// order, 32 windows per load, and finishes the components.
+// ---------------------------------------------------------------------------
+constexpr int kRedWarps = 8;
+
+__device__ __forceinline__ bool reduce_in_parallel(const EncodeParams &p) {
+    return p.uniformBlocks > 0 && (p.uniformBlocks / 3) % kRedWin == 0 && p.winMM != nullptr;
+}
+
+__device__ __forceinline__ void reduce_windows(const EncodeParams &p, int lane, int k) {
+    const int64_t nWin = p.nBlocks / kRedWin;  // (uniform batch: nBlocks is a multiple of kRedWin)
+    uint4 cur[8];
+    for (int64_t w = k; w < nWin; w += kRedWarps) {
+        const int64_t base = w * kRedWin;
+        red_load(p, base, lane, cur);
+        SpinClock clk;
+        while (true) {
+            bool all = true;
+#pragma unroll
+            for (int j = 0; j < 8; j++) all = all && mm_ready(cur[j]);
+            if (__all_sync(kFull, all)) break;
+            if (spin_expired(clk)) {
+                if (lane == 0) spin_timeout(p.error, 6, base);
+                return;
+            }
+            if (clk.spins > 4) __nanosleep(200);
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                if (!mm_ready(cur[j])) cur[j] = ld_relaxed_u4(p.blkMM + base + j * 64 + lane * 2);
+        }
+        uint32_t lo = 0xffffffffu, hi = 0xffffffffu;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            lo = min(lo, min(cur[j].x, cur[j].z));
+            hi = min(hi, min(cur[j].y, cur[j].w));
+        }
+        lo = __reduce_min_sync(kFull, lo);
+        hi = __reduce_min_sync(kFull, hi);
+        if (lane == 0)
+            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p.winMM + w), "l"((uint64_t)lo | ((uint64_t)hi << 32)) : "memory");
+    }
+}
+
+__device__ __forceinline__ void reduce_fold(const EncodeParams &p, int lane) {
+    const int64_t nWin = p.nBlocks / kRedWin;
+    RedWalk w;
+    w.f = w.comp = 0;
+    w.compEnd = 0;
+    w.lo = w.hi = 0xffffffffu;
+    red_skip_empty(p, w);
+    for (int64_t w0 = 0; w0 < nWin; w0 += 32) {
+        const int cnt = (int)min((int64_t)32, nWin - w0);
+        // windows are folded as they arrive: waiting for the whole batch of 32 would wait
+        // for A work that itself waits (through the ring) for the parameters of this field
+        uint64_t v = 0;
+        int done = 0;
+        SpinClock clk;
+        while (done < cnt) {
+            if (lane >= done && lane < cnt && v == 0) v = ld_relaxed_u64(p.winMM + w0 + lane);
+            const unsigned ok = __ballot_sync(kFull, lane < cnt && v != 0);
+            int upto = done;
+            while (upto < cnt && ((ok >> upto) & 1u)) upto++;
+            for (int i = done; i < upto; i++) {
+                const uint64_t x = __shfl_sync(kFull, v, i);
+                w.lo = min(w.lo, (uint32_t)x);
+                w.hi = min(w.hi, (uint32_t)(x >> 32));
+                if ((w0 + i + 1) * kRedWin == w.compEnd) red_finish_comp(p, w, lane);
+            }
+            if (upto == done) {
+                if (spin_expired(clk)) {
+                    if (lane == 0) spin_timeout(p.error, 6, (w0 + done) * kRedWin);
+                    return;
+                }
+                __nanosleep(200);
+            }
+            done = upto;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
 // A work: min/max of one block
 // ---------------------------------------------------------------------------
 template <bool kPos>
@@ -324,6 +422,11 @@ __device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d
     uw.tLo = d.tLo;
     uw.L = d.L;
     float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+#if defined(MNW_ABLATE) && (MNW_ABLATE & 8)
+    if (true) {  // timing experiment only: one value per lane instead of 32
+        lo = hi = stage[lane];
+    } else
+#endif
     if (!(d.flags & kDescSlow)) {
         const float4 *st = reinterpret_cast<const float4 *>(stage);
         minmax_stage<false>(st, lane, uw, lo, hi);

@@ -93,7 +93,11 @@ __device__ __forceinline__ void quantise32(const Unwrap &uw, float x0, double sc
         float u = __uint_as_float(q[i]);
         if (kPos) u = unwrap_t(u, uw);
         const float a = __fsub_rn(u, x0);
+#if defined(MNW_ABLATE) && (MNW_ABLATE & 1)
+        const float s = __fmul_rn(a, (float)scale);  // timing experiment only: not the exact quotient
+#else
         const float s = __double2float_rn(__dmul_rn((double)a, scale));
+#endif
         if (kBiased) q[i] = __float_as_uint(__fadd_rz(fminf(s, topf), 8388608.0f));
         else q[i] = min(__float2uint_rz(s), top);
     }

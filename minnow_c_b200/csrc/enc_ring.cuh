@@ -1,22 +1,23 @@
-// enc_ring.cuh -- the input ring of k_encode. The producer warp of a CTA draws
-// group tickets; each of its 32 lanes owns one slot of the group: it works out
-// the slot's block, waits for the next ring stage to be free, writes the work
-// descriptor next to it and has the TMA unit copy the block's 4 KiB into the
-// stage (2D tensor map over the input as rows of 32 floats, 128-byte swizzle,
-// so that a consumer lane can read its 32 consecutive values without bank
-// conflicts). Consumer warps claim stages in order, wait on the stage's "full"
-// mbarrier and hand the stage back through its "empty" mbarrier. A parity wait
-// can only tell the current phase from the one before, and consumers racing
-// through no-op slots can claim the next use of a stage whose current fill is
-// still in flight: so a consumer first waits until the stage's previous use has
-// been handed back (a plain counter), and only then for the fill.
+// enc_ring.cuh -- the input ring of k_encode. The planner warp of a CTA draws
+// group tickets; each of its 32 lanes owns one slot of the group: it works out the
+// slot's block and writes the work descriptor into a queue indexed by sequence
+// number. The issuer (one thread) walks the sequence numbers in order and, the
+// moment the next one's ring stage has been handed back, has the TMA unit copy the
+// block's 4 KiB into the stage (2D tensor map over the input as rows of 32 floats,
+// 128-byte swizzle, so that a consumer lane can read its 32 consecutive values
+// without bank conflicts). Consumer warps claim sequence numbers in order, wait on
+// the stage's "full" mbarrier and hand the stage back through its "empty" mbarrier.
+// A parity wait can only tell the current phase from the one before, and consumers
+// racing through no-op slots can claim the next use of a stage whose current fill is
+// still in flight: so a consumer first waits until the stage's previous use has been
+// handed back (a plain counter), and only then for the fill.
 #pragma once
 
 #include "enc_math.cuh"
 
 namespace mnw {
 
-struct WorkDesc {  // 80 bytes, one per ring stage: the block and what its component needs
+struct WorkDesc {  // 80 bytes, one per sequence number (queue of kDescQ): the block and what its component needs
     int32_t kind;
     int32_t f, comp, b;
     int64_t blk;
@@ -29,7 +30,7 @@ struct WorkDesc {  // 80 bytes, one per ring stage: the block and what its compo
     float L;
     uint32_t pad;
     int64_t payBase;  // byte offset of the field's payload area if the batch's prefix were 0
-    int64_t pad2;
+    int64_t row;      // first row of the block in the tensor map (the issuer's TMA coordinate)
 };
 enum : uint32_t {
     kDescSlow = 1u,   // the block did not go through the TMA: the consumer loads it itself
@@ -40,9 +41,11 @@ enum : uint32_t {
 struct RingCtrl {
     uint64_t *full;   // [kEncStages] descriptor written and TMA bytes landed
     uint64_t *empty;  // [kEncStages] the consumer is done with the stage
-    WorkDesc *desc;   // [kEncStages]
-    uint32_t *qHead;  // next stage sequence number to claim (consumers, atomic)
+    WorkDesc *desc;   // [kDescQ] by sequence number modulo kDescQ
+    uint32_t *qHead;  // [0] next sequence number to claim (consumers, atomic); [1] sequence numbers planned
+                      // (planner); [2] issued (issuer); [3] one past the last sequence number, once known
     volatile uint32_t *uses;  // [kEncStages] how many times the stage has been handed back
+    long long *tIssue, *tRel;  // MNWCUDA_ENCODE_STATS: per stage, clock of the last fill / hand-back (else null)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -98,7 +101,26 @@ __device__ __forceinline__ void tma_load_block_plain(void *smemDst, const CUtens
         "l"(reinterpret_cast<uint64_t>(map)), "r"(0), "r"(row), "r"(smem_u32(bar))
         : "memory");
 }
+// ask L2 for a block ahead of its TMA copy (no completion tracking: a hint)
+__device__ __forceinline__ void tma_prefetch_block(const CUtensorMap *map, int32_t row) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(map)),
+                 "r"(0), "r"(row)
+                 : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// atomicAdd on a shared word by one elected lane, result to all lanes (inline asm: the
+// compiler otherwise wraps a one-lane atomicAdd in its warp-aggregation sequence)
+__device__ __forceinline__ uint32_t warp_atom_add_shared(uint32_t *word, uint32_t v) {
+    uint32_t old = 0;
+    asm volatile("{\n\t"
+                 ".reg .pred one;\n\t"
+                 "elect.sync _|one, 0xffffffff;\n\t"
+                 "@one atom.shared.add.u32 %0, [%1], %2;\n\t"
+                 "}"
+                 : "+r"(old) : "r"((uint32_t)__cvta_generic_to_shared(word)), "r"(v) : "memory");
+    return __shfl_sync(0xffffffffu, old, 0);
+}
 
 __device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
     RingCtrl rc;
@@ -106,21 +128,23 @@ __device__ __forceinline__ RingCtrl ring_ctrl(uint8_t *smem) {
     rc.full = reinterpret_cast<uint64_t *>(c);
     rc.empty = rc.full + kEncStages;
     rc.desc = reinterpret_cast<WorkDesc *>(rc.empty + kEncStages);
-    rc.qHead = reinterpret_cast<uint32_t *>(rc.desc + kEncStages);
+    rc.qHead = reinterpret_cast<uint32_t *>(rc.desc + kDescQ);
     rc.uses = rc.qHead + 4;
+    rc.tIssue = rc.tRel = nullptr;
     return rc;
 }
 
 // ---------------------------------------------------------------------------
-// producer warp: all 32 lanes, one slot each per pass
+// planner warp: all 32 lanes, one slot each per pass. It draws the group tickets,
+// works out the 32 descriptors of a pass (block location, component constants,
+// unwrap thresholds, the published quantisation parameters: global loads) and puts
+// them into the descriptor queue, up to kDescQ - kEncStages sequence numbers ahead
+// of the issuer. It never touches the ring: a stage that has been handed back must
+// not wait for descriptor arithmetic.
 // ---------------------------------------------------------------------------
-template <bool kFromQ>
-__device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMap *map, uint8_t *smem,
-                                         const RingCtrl &rc, int lane) {
-    // A reads carry no cache hint, B reads are evict_first: with the B work ~56 MB of
-    // A traffic behind, about two thirds of the B reads still hit in L2 (evict_last on
-    // the A reads thrashes: nothing survives; MNWCUDA_DBG=2 tries it, 8 streams both)
-    const uint64_t keep = l2_policy_keep(), drop = l2_policy_drop();
+template <bool kFromQ, bool kStats>
+__device__ __forceinline__ void planner(const EncodeParams &p, const CUtensorMap *map, const RingCtrl &rc, int lane,
+                                        int nConsumers) {
     const bool onlyB = kFromQ || p.lagG < 0;
     struct {
         int f, comp;
@@ -132,13 +156,16 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
     pc.flags = pc.depth = 0;
     pc.L = pc.tHi = pc.tLo = pc.x0 = 0.0f;
     pc.scale = 0.0;
+    volatile uint32_t *planned = rc.qHead + 1, *issued = rc.qHead + 2, *end = rc.qHead + 3;
     uint32_t pass = 0;
     uint32_t tk = 0;
     if (lane == 0) tk = atomicAdd(p.ticket, 1u);
+    bool stop = false;
     while (true) {
         const int64_t g = (int64_t)__shfl_sync(kFull, tk, 0);
-        if (g >= p.nGroups) break;
-        if (lane == 0) tk = atomicAdd(p.ticket, 1u);  // the next ticket is on its way meanwhile
+        stop = g >= p.nGroups;
+        if (!stop && lane == 0) tk = atomicAdd(p.ticket, 1u);  // the next ticket is on its way meanwhile
+        const long long tp0 = kStats ? clock64() : 0;
         WorkDesc d;
         d.kind = kWorkNop;
         d.f = d.comp = d.b = 0;
@@ -148,9 +175,11 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
         d.x0 = d.tHi = d.tLo = d.L = 0.0f;
         d.depth = 0;
         d.pad = 0;
-        d.payBase = d.pad2 = 0;
-        int64_t blk;
-        if (onlyB) {
+        d.payBase = d.row = 0;
+        int64_t blk = -1;
+        if (stop) {
+            if (lane < nConsumers) d.kind = kWorkStop;  // the last pass: one stop marker per consumer warp
+        } else if (onlyB) {
             blk = g * kGroupSlots + lane;
             if (blk < p.nBlocks) d.kind = kWorkB;
         } else if (lane < kGroupBlocks) {
@@ -161,18 +190,16 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
             if (blk >= 0 && blk < p.nBlocks) d.kind = kWorkB;
         }
         d.blk = blk;
-        bool fast = false;
-        int64_t row = 0;
-        if (d.kind != kWorkNop) {
+        if (d.kind == kWorkA || d.kind == kWorkB) {
             locate_block(p, blk, d.f, d.comp, d.b);
             const DevField *fdp = p.fields + d.f;
             const int n = fdp->n;
             d.len = min(kBlockLen, n - d.b * kBlockLen);
             d.payBase = fdp->fixedBase + 64 + (int64_t)fdp->nb * 48;
             const int64_t off = fdp->ioOff + (int64_t)d.comp * n + (int64_t)d.b * kBlockLen;  // floats from p.in
-            row = (p.tmaShift + off) >> 5;
-            fast = !kFromQ && p.tmaShift >= 0 && d.len == kBlockLen && ((p.tmaShift + off) & 31) == 0 &&
-                   row + 32 <= p.tmaRows;
+            d.row = (p.tmaShift + off) >> 5;
+            const bool fast = !kFromQ && p.tmaShift >= 0 && d.len == kBlockLen && ((p.tmaShift + off) & 31) == 0 &&
+                              d.row + 32 <= p.tmaRows;
             // the component's constants: this lane sees the same component for many passes
             if (pc.f != d.f || pc.comp != d.comp) {
                 pc.f = d.f;
@@ -209,6 +236,9 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                     pc.flags |= kDescQuant;
                 }
             }
+            // MNWCUDA_DBG & 16 / & 32: L2 prefetch of the A / B blocks at planning time (experiment)
+            if (fast && ((d.kind == kWorkA && (p.dbg & 16)) || (d.kind == kWorkB && (p.dbg & 32))))
+                tma_prefetch_block(map, (int32_t)d.row);
             d.flags = pc.flags | (fast ? 0u : kDescSlow);
             d.scale = pc.scale;
             d.x0 = pc.x0;
@@ -217,30 +247,86 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
             d.tLo = pc.tLo;
             d.L = pc.L;
         }
+        // room in the queue: an entry is free once its stage's next use can be issued
         const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
+        const long long tp1 = kStats ? clock64() : 0;
+        for (SpinClock clk; pass * kGroupSlots + kGroupSlots > *issued + (uint32_t)(kDescQ - kEncStages);) {
+            __nanosleep(64);
+            if (spin_expired(clk)) { spin_timeout(p.error, 8, -1); return; }
+        }
+        rc.desc[seq % kDescQ] = d;
+        __threadfence_block();
+        __syncwarp();
+        if (lane == 0) {
+            *planned = (pass + 1) * kGroupSlots;
+            if (stop) *end = (pass + 1) * kGroupSlots;
+        }
+        if (kStats && p.stats && lane == 0) {
+            atomicAdd(p.stats + 22, (unsigned long long)(tp1 - tp0));
+            atomicAdd(p.stats + 23, (unsigned long long)(clock64() - tp1));
+            atomicAdd(p.stats + 24, 1ull);
+        }
+        pass++;
+        if (stop) return;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// issuer warp: lane l owns the sequence numbers l, l + 32, ... Round by round, every
+// lane starts the TMA copy of its block the moment its ring stage has been handed
+// back (or just completes the stage's "full" barrier for a block that does not go
+// through the TMA); a lane does not wait for the slowest stage of the round (a B
+// block holds one longer than an A block). Nothing else happens on this path: the
+// descriptors were worked out ahead of time by the planner.
+// ---------------------------------------------------------------------------
+template <bool kStats>
+__device__ __forceinline__ void issuer(const EncodeParams &p, const CUtensorMap *map, uint8_t *smem,
+                                       const RingCtrl &rc, int lane) {
+    // A reads carry no cache hint, B reads are evict_first: with the B work ~56 MB of
+    // A traffic behind, about two thirds of the B reads still hit in L2 (evict_last on
+    // the A reads thrashes: nothing survives)
+    const uint64_t drop = l2_policy_drop();
+    volatile uint32_t *planned = rc.qHead + 1, *issued = rc.qHead + 2, *end = rc.qHead + 3;
+    long long refill = 0, nRefill = 0;
+    for (uint32_t round = 0;; round++) {
+        const uint32_t seq = round * kGroupSlots + (uint32_t)lane;
+        for (SpinClock clk; (round + 1) * kGroupSlots > *planned;) {
+            if (round * kGroupSlots >= *end) {
+                if (kStats && p.stats) {
+                    atomicAdd(p.stats + 20, (unsigned long long)refill);
+                    atomicAdd(p.stats + 21, (unsigned long long)nRefill);
+                }
+                return;
+            }
+            if (spin_expired(clk)) { spin_timeout(p.error, 9, -1); return; }
+        }
+        __threadfence_block();
         const int s = (int)(seq % kEncStages);
         const uint32_t use = seq / kEncStages;
-        // every lane fills its stage the moment that stage is handed back: a lane must
-        // not wait for the slowest stage of the pass (a B block holds one ten times
-        // longer than an A block)
+        const WorkDesc *d = rc.desc + seq % kDescQ;
+        const int kind = d->kind;
+        const bool fast = (kind == kWorkA || kind == kWorkB) && !(d->flags & kDescSlow);
+        const int32_t row = (int32_t)d->row;
         bool filled = false;
         unsigned long long t0 = 0;
         for (uint32_t spins = 0;; spins++) {
-            if (!filled && (use == 0 || mbar_try_wait(rc.empty + s, (use - 1) & 1))) {
-                rc.desc[s] = d;
+            if (!filled && (use == 0 || (rc.uses[s] >= use && mbar_try_wait(rc.empty + s, (use - 1) & 1)))) {
+                if (kStats && rc.tIssue) {
+                    const long long now = clock64();
+                    if (use > 0) { refill += now - rc.tRel[s]; nRefill++; }
+                    rc.tIssue[s] = now;
+                }
                 if (fast) {
                     mbar_arrive_expect_tx(rc.full + s, kEncStageBytes);
-                    if (d.kind == kWorkA && !(p.dbg & 10))
-                        tma_load_block_plain(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s);
-                    else
-                        tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, (int32_t)row, rc.full + s,
-                                       (d.kind == kWorkA && (p.dbg & 2)) ? keep : drop);
+                    if (kind == kWorkA) tma_load_block_plain(smem + kEncRingOff + s * kEncStageBytes, map, row, rc.full + s);
+                    else tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, row, rc.full + s, drop);
                 } else {
                     mbar_arrive(rc.full + s);
                 }
                 filled = true;
             }
             if (__all_sync(kFull, filled)) break;
+            __nanosleep(32);  // (a hot spin would take issue slots from the consumers of this scheduler)
             if ((spins & 1023u) == 1023u) {  // bounded like every other wait
                 unsigned long long t;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -251,25 +337,7 @@ __device__ __forceinline__ void producer(const EncodeParams &p, const CUtensorMa
                 }
             }
         }
-        pass++;
-    }
-    if (lane < kEncConsumers) {  // one stop marker per consumer warp
-        const uint32_t seq = pass * kGroupSlots + (uint32_t)lane;
-        const int s = (int)(seq % kEncStages);
-        const uint32_t use = seq / kEncStages;
-        if (use > 0 && !mbar_wait(p.error, rc.empty + s, (use - 1) & 1, 4)) return;
-        WorkDesc d;
-        d.kind = kWorkStop;
-        d.f = d.comp = d.b = 0;
-        d.blk = -1;
-        d.len = 0;
-        d.flags = kDescSlow;
-        d.scale = 0.0;
-        d.x0 = d.tHi = d.tLo = d.L = 0.0f;
-        d.depth = d.pad = 0;
-        d.payBase = d.pad2 = 0;
-        rc.desc[s] = d;
-        mbar_arrive(rc.full + s);
+        if (lane == 0) *issued = (round + 1) * kGroupSlots;
     }
 }
 

@@ -195,8 +195,8 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
             MNW_PANIC("cuTensorMapEncodeTiled is not available from this driver.");
     }
     if (getenv("MNWCUDA_ENCODE_STATS")) {
-        CUDA_CHECK(cudaMalloc(&ctx->encStats, 128));
-        CUDA_CHECK(cudaMemset(ctx->encStats, 0, 128));
+        CUDA_CHECK(cudaMalloc(&ctx->encStats, 256));
+        CUDA_CHECK(cudaMemset(ctx->encStats, 0, 256));
     }
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
@@ -228,8 +228,15 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
         if (e) cudaEventDestroy(e);
     if (ctx->tabEv) cudaEventDestroy(ctx->tabEv);
     if (ctx->encStats) {
-        unsigned long long h[16];
+        unsigned long long h[32];
         cudaMemcpy(h, ctx->encStats, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[mnwcuda encode stats] stage timeline (clk): fill issued -> consumer has the data %.0f | "
+                        "handed back -> refilled %.0f | producer per pass: descriptors %.0f, filling %.0f (%llu passes)\n",
+                (double)h[16] / (double)(h[17] ? h[17] : 1), (double)h[20] / (double)(h[21] ? h[21] : 1),
+                (double)h[22] / (double)(h[24] ? h[24] : 1), (double)h[23] / (double)(h[24] ? h[24] : 1), h[24]);
+        fprintf(stderr, "[mnwcuda encode stats] service warps: scan windows %llu, complete at first look %.1f%% | reduce windows "
+                        "%llu, complete at first look %.1f%% (100%%: the warp never waits, everybody waits for it)\n",
+                h[25], 100.0 * (double)h[26] / (double)(h[25] ? h[25] : 1), h[27], 100.0 * (double)h[28] / (double)(h[27] ? h[27] : 1));
         const double tot = (double)h[7] > 0 ? (double)h[7] : 1.0;
         fprintf(stderr, "[mnwcuda encode stats] consumer-time shares: A %.1f%% B %.1f%% queue %.1f%% | clk/A-block %.0f "
                         "clk/B-block %.0f | blocks A %llu B %llu\n",
@@ -306,6 +313,15 @@ extern "C" int mnwcuda_Status(MnwCudaCtx *ctx, void *stream) {
                 while (iFq < fq.size() && (fq[iFq] >> 63)) iFq++;
                 fprintf(stderr, "[mnwcuda] first missing: prefix %zu size %zu (missing in all %zu) minmax %zu params word %zu of %zu\n",
                         iPre, iAgg, nAggMissing, iMM, iFq, fq.size());
+                if (q.winMM) {
+                    std::vector<uint64_t> wm(nb / kRedWin + 1);
+                    cudaMemcpy(wm.data(), q.winMM, (nb / kRedWin) * 8, cudaMemcpyDeviceToHost);
+                    size_t iW = 0, nMiss = 0;
+                    while (iW < nb / kRedWin && wm[iW]) iW++;
+                    for (size_t i = 0; i < nb / kRedWin; i++) nMiss += !wm[i];
+                    fprintf(stderr, "[mnwcuda] reduce windows: first missing %zu (missing in all %zu of %zu)\n", iW, nMiss,
+                            nb / kRedWin);
+                }
             }
         }
         CUDA_CHECK(cudaMemsetAsync(ctx->error, 0, sizeof(int), s));
@@ -387,8 +403,9 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     const size_t padScan = nWin * kScanWin;
     const size_t padRed = (size_t)((pl.nBlocks + kRedWin - 1) / kRedWin) * kRedWin;
     const size_t bWin = ((nWin + 1) * 8 + 15) & ~(size_t)15, bMM = padRed * 8, bFq = nF * 6 * 8;
-    const size_t bRel = padScan * 4, bAgg = padScan * 2;
-    const size_t stateBytes = bWin + bMM + bFq + bRel + bAgg + 16;
+    const size_t bRel = padScan * 4, bAgg = ((padScan * 2 + 15) & ~(size_t)15) + 16;
+    const size_t bWinMM = (padRed / kRedWin) * 8;
+    const size_t stateBytes = bWin + bMM + bFq + bRel + bAgg + bWinMM;
     p.tbl = static_cast<uint4 *>(ctx->misc.need((size_t)(pl.nBlocks + 1) * sizeof(uint4)));
     uint8_t *st = static_cast<uint8_t *>(ctx->tileState.need(stateBytes));
     p.winBase = reinterpret_cast<uint64_t *>(st);
@@ -396,7 +413,8 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     p.fq = reinterpret_cast<uint64_t *>(st + bWin + bMM);
     p.blkRel = reinterpret_cast<uint32_t *>(st + bWin + bMM + bFq);
     p.blkAgg = reinterpret_cast<uint16_t *>(st + bWin + bMM + bFq + bRel);
-    p.ticket = reinterpret_cast<uint32_t *>(st + bWin + bMM + bFq + bRel + bAgg);
+    p.ticket = reinterpret_cast<uint32_t *>(st + bWin + bMM + bFq + bRel + bAgg - 16);
+    p.winMM = reinterpret_cast<uint64_t *>(st + bWin + bMM + bFq + bRel + bAgg);
     p.out = d_out;
     p.outCap = outCap;
     p.offsets = d_offsets;
