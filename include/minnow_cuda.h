@@ -225,6 +225,35 @@ int32_t mnwcuda_SegmentFromImage(MnwCudaCtx *ctx, const uint8_t *h_image, int64_
                                  CField *fields, int32_t maxFields, int32_t *valid,
                                  int32_t *particleNum);
 
+/* ---- decode of one float field without any allocation ----
+ * No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it). The same kernels as
+ * mnwcuda_DecodeFieldsDev with nFields = 1, but every piece of decoder scratch
+ * (control words, parsed header, jump-matrix powers, damaged-task list, dither
+ * stream states) lives in one file-scope `static __device__` array of
+ * MNWCUDA_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit; no context is needed and the call issues kernel launches only (no
+ * cudaMalloc / cudaFree / copies; the FIRST call on a device also resolves the
+ * array with cudaGetSymbolAddress and uploads 52 KiB of jump-matrix powers with
+ * a synchronous cudaMemcpy -- make that call outside any capture).
+ * d_payload: the field's algo_Diff payload on the device, 16-byte aligned,
+ * payloadLen bytes; d_out: 3 * particleLen floats (planar, as DecodeFieldsDev);
+ * d_status: device word that receives 0 or the device-side error (3 = malformed
+ * payload), may be NULL; `device` < 0 = the current device.
+ * Returns 0, -1 bad argument, -3 field code other than Posn / Velc, -6
+ * misaligned pointer, -7 particleLen > MNWCUDA_NOALLOC_MAX_PARTICLES (message on
+ * stderr; use mnwcuda_DecodeFieldsDev), -8 CUDA error. Work is enqueued on
+ * `stream`, not waited for. All calls on a device share the one array: calls
+ * that overlap on the GPU (different streams, or several threads) race -- keep
+ * them on one stream or order them with events. */
+#define MNWCUDA_NOALLOC_MAX_PARTICLES (1 << 22)
+#define MNWCUDA_NOALLOC_SCRATCH_BYTES 253184
+int mnwcuda_DecodeFieldNoAlloc(int device, const uint8_t *d_payload,
+                               int64_t payloadLen, int32_t particleLen,
+                               uint32_t fieldCode, float *d_out,
+                               int32_t *d_status, void *stream);
+
 /* ---- synthetic input (bench/tests): Zel'dovich-displaced Lagrangian grid,
  * ids [firstId, firstId+count) of an ngrid^3 box, planar float32.
  * d_pos / d_vel may be NULL. ---- */

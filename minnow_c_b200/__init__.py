@@ -170,7 +170,10 @@ EXPORTS = {
                                              C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "mnwcuda_GenerateZeldovichRough": (C.c_int, [C.c_void_p, C.c_int32, C.c_float, C.c_uint64, C.c_int64, C.c_int64,
                                                  C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mnwcuda_DecodeFieldNoAlloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]),
 }
+NOALLOC_MAX_PARTICLES = 1 << 22  # MNWCUDA_NOALLOC_MAX_PARTICLES
 
 class _Seq(C.Structure):
     _fields_ = [("Data", C.c_void_p), ("Len", C.c_int32), ("Cap", C.c_int32)]

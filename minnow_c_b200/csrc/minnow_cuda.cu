@@ -978,3 +978,5 @@ extern "C" int mnwcuda_GenerateZeldovichRough(MnwCudaCtx *ctx, int32_t ngrid, fl
     CUDA_CHECK(cudaGetLastError());
     return 0;
 }
+
+#include "minnow_noalloc.inl"
