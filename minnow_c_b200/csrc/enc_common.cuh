@@ -23,6 +23,9 @@
 namespace mnw {
 
 constexpr unsigned kFull = 0xffffffffu;
+#ifndef MNW_EXP
+#define MNW_EXP 3  // experiment switches (bit 0: lane-class unwrap in B work, bit 1: unconditional arena chunks)
+#endif
 #ifndef MNW_ENC_CONSUMERS
 #define MNW_ENC_CONSUMERS 18
 #endif

@@ -81,8 +81,15 @@ __device__ __forceinline__ int arena_alloc(ParkFifo &ff, int need, int &span) {
     return start;
 }
 
-// 16-byte chunk c of a packed block in the arena (skewed layout, zero beyond the block's words)
+// 16-byte chunk c of a packed block in the arena (skewed layout). The pack routines
+// write all 32 x width words of a block -- a multiple of four -- and the residuals
+// beyond a ragged block's length are zero, so the words past the block's last one
+// are there and zero; four words starting at a multiple of four share a skew row.
 __device__ __forceinline__ uint4 arena_chunk(const uint32_t *src, int c, int nWords) {
+#if MNW_EXP & 2
+    const uint32_t *w = src + skew(c * 4);
+    return make_uint4(w[0], w[1], w[2], w[3]);
+#else
     const int m = c * 4;
     uint4 o;
     o.x = src[skew(m)];
@@ -90,6 +97,7 @@ __device__ __forceinline__ uint4 arena_chunk(const uint32_t *src, int c, int nWo
     o.z = m + 2 < nWords ? src[skew(m + 2)] : 0u;
     o.w = m + 3 < nWords ? src[skew(m + 3)] : 0u;
     return o;
+#endif
 }
 
 // the oldest block that still sits in the arena moves to its record's scratch slot
@@ -98,6 +106,7 @@ __device__ __forceinline__ void spill_oldest_resident(ParkFifo &ff, int lane) {
     const int4 wh = ff.where[k];
     uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
     const uint32_t *src = ff.arena + wh.x;
+#pragma unroll 1
     for (int c = lane; c < wh.w; c += 32) slot[c] = arena_chunk(src, c, wh.z);
     __syncwarp();
     if (lane == 0) ff.where[k] = make_int4(-1, 0, wh.z, wh.w);
@@ -121,9 +130,11 @@ __device__ __forceinline__ void place_finish(const EncodeParams &p, ParkFifo &ff
         uint4 *dst = reinterpret_cast<uint4 *>(p.out + dstByte);
         if (wh.x >= 0) {
             const uint32_t *src = ff.arena + wh.x;
+#pragma unroll 1
             for (int c = lane; c < size16; c += 32) st_stream_u4(dst + c, arena_chunk(src, c, wh.z));
         } else {
             const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)k * kSlotWords);
+#pragma unroll 1
             for (int c = lane; c < size16; c += 32) st_stream_u4(dst + c, __ldcg(slot + c));
         }
     }

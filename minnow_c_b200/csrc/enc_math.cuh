@@ -83,15 +83,49 @@ __device__ __forceinline__ void load_block32(const float *stage, int lane, uint3
     }
 }
 
+// util_UndoPeriodic on the lane's 32 values, in place. unwrap_t is monotone within
+// each of its three classes (x >= tHi: x - L; x < tLo: x + L; between: x), so a lane
+// whose raw extrema fall into one class shifts all of its values alike -- and in
+// nearly every block no lane needs a shift at all: one three-input min/max per two
+// values instead of five instructions per value. Lanes that straddle a threshold
+// (or hold a NaN) take the value-by-value form; the warp votes so that the common
+// case has no divergent code.
+__device__ __forceinline__ void unwrap32(const Unwrap &uw, uint32_t (&q)[kChunk]) {
+    float lo = __uint_as_float(q[0]), hi = lo;
+#pragma unroll
+    for (int i = 1; i < kChunk - 1; i += 2) {
+        lo = fminf(lo, fminf(__uint_as_float(q[i]), __uint_as_float(q[i + 1])));
+        hi = fmaxf(hi, fmaxf(__uint_as_float(q[i]), __uint_as_float(q[i + 1])));
+    }
+    lo = fminf(lo, __uint_as_float(q[kChunk - 1]));
+    hi = fmaxf(hi, __uint_as_float(q[kChunk - 1]));
+    const bool split = (lo < uw.tHi && !(hi < uw.tHi)) || (lo < uw.tLo && !(hi < uw.tLo)) || !(lo <= hi);
+    const float shift = !(lo < uw.tHi) ? -uw.L : lo < uw.tLo ? uw.L : 0.0f;
+    if (__any_sync(kFull, split)) {
+#pragma unroll
+        for (int i = 0; i < kChunk; i++) q[i] = __float_as_uint(unwrap_t(__uint_as_float(q[i]), uw));
+    } else if (__any_sync(kFull, shift != 0.0f)) {
+        // RN(x + (-L)) = RN(x - L); a lane of the middle class adds +0 (x itself, and -0 -> +0
+        // quantises like -0: both give index 0 or the same difference to x0)
+#pragma unroll
+        for (int i = 0; i < kChunk; i++) q[i] = __float_as_uint(__fadd_rn(__uint_as_float(q[i]), shift));
+    }
+}
+
 // in place: q holds the raw floats' bit patterns on entry, the indices on return
 template <bool kPos, bool kBiased>
 __device__ __forceinline__ void quantise32(const Unwrap &uw, float x0, double scale, uint32_t top,
                                            uint32_t (&q)[kChunk]) {
     const float topf = (float)top;
+#if MNW_EXP & 1
+    if (kPos) unwrap32(uw, q);
+#endif
 #pragma unroll
     for (int i = 0; i < kChunk; i++) {
         float u = __uint_as_float(q[i]);
+#if !(MNW_EXP & 1)
         if (kPos) u = unwrap_t(u, uw);
+#endif
         const float a = __fsub_rn(u, x0);
 #if defined(MNW_ABLATE) && (MNW_ABLATE & 1)
         const float s = __fmul_rn(a, (float)scale);  // timing experiment only: not the exact quotient

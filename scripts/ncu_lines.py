@@ -30,7 +30,12 @@ rows = list(csv.reader(raw.splitlines()))
 hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 hdr = rows[hi]
 ix = {n: hdr.index(n) for n in ("Address", "Source", "# Samples", "Instructions Executed")}
-body = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+body = []
+for r in rows[hi + 1:]:  # the first kernel of the report only
+    if r and r[0] == "Address":
+        break
+    if len(r) == len(hdr):
+        body.append(r)
 base = int(body[0][ix["Address"]], 16)
 agg = collections.defaultdict(lambda: [0, 0])
 tot = [0, 0]
