@@ -27,7 +27,7 @@ constexpr unsigned kFull = 0xffffffffu;
 #define MNW_EXP 3  // experiment switches (bit 0: lane-class unwrap in B work, bit 1: unconditional arena chunks)
 #endif
 #ifndef MNW_ENC_CONSUMERS
-#define MNW_ENC_CONSUMERS 18
+#define MNW_ENC_CONSUMERS 22
 #endif
 constexpr int kEncConsumers = MNW_ENC_CONSUMERS;
 constexpr int kEncWarps = kEncConsumers + 2;  // per CTA (one CTA per SM): planner, issuer, consumers; the last warp of CTA 0 is the scan

@@ -1,5 +1,5 @@
 // enc_kernel.cuh -- k_encode (persistent, one CTA per SM: a TMA producer warp,
-// 18 consumer warps, a service warp: scan in CTA 0, reduce in CTA 1) and k_finalize.
+// 22 consumer warps, a service warp: scan in CTA 0, reduce in CTA 1) and k_finalize.
 //
 //   A work   util_UndoPeriodic + util_MinMax of one block (src/util.c:97-113,
 //            27-46) straight out of the ring; the block's min/max go out as
