@@ -23,16 +23,16 @@
 namespace mnw {
 
 constexpr unsigned kFull = 0xffffffffu;
-#ifndef MNW_EXP
-#define MNW_EXP 3  // experiment switches (bit 0: lane-class unwrap in B work, bit 1: unconditional arena chunks)
-#endif
 #ifndef MNW_ENC_CONSUMERS
 #define MNW_ENC_CONSUMERS 22
 #endif
 constexpr int kEncConsumers = MNW_ENC_CONSUMERS;
 constexpr int kEncWarps = kEncConsumers + 2;  // per CTA (one CTA per SM): planner, issuer, consumers; the last warp of CTA 0 is the scan
                                               // warp, of CTA 1 the reduce warp (elsewhere it is a consumer like the others)
-constexpr int kDescQ = 96;           // descriptor queue: the planner runs up to kDescQ - kEncStages slots ahead of the issuer
+#ifndef MNW_DESCQ
+#define MNW_DESCQ 96
+#endif
+constexpr int kDescQ = MNW_DESCQ;           // descriptor queue: the planner runs up to kDescQ - kEncStages slots ahead of the issuer
 constexpr int kEncStageBytes = 4096;
 constexpr int kGroupSlots = 32;      // slots per ticket
 constexpr int kGroupBlocks = 16;     // A blocks (and B blocks) per group
@@ -43,7 +43,12 @@ constexpr int kArenaWords = 832;     // per consumer: packed blocks waiting for 
 // next to the consumers' arenas and records
 constexpr int kEncPerConsumer = kFifo * (16 + 8 + 8) + 64 + kArenaWords * 4;
 constexpr int kEncTimelineBytes = 1024;  // MNWCUDA_ENCODE_STATS: issue / hand-back clocks of up to 64 stages
-constexpr int kEncStages = (232448 - 32 - kEncTimelineBytes - kDescQ * 80 - kEncConsumers * kEncPerConsumer) / (kEncStageBytes + 2 * 8 + 4);
+constexpr int kEncStagesFit = (232448 - 32 - kEncTimelineBytes - kDescQ * 80 - kEncConsumers * kEncPerConsumer) / (kEncStageBytes + 2 * 8 + 4);
+#ifdef MNW_ENC_STAGES
+constexpr int kEncStages = MNW_ENC_STAGES;
+#else
+constexpr int kEncStages = kEncStagesFit;
+#endif
 constexpr int kEncRingOff = 0;
 constexpr int kEncCtrlOff = kEncStages * kEncStageBytes;
 constexpr int kEncCtrlBytes = (2 * kEncStages * 8 + kDescQ * 80 + 16 + kEncStages * 4 + 15) & ~15;

@@ -17,12 +17,14 @@ __device__ __forceinline__ void release_stage(const RingCtrl &rc, int s, bool wr
 }
 
 // the producer found the component's parameters not yet published: wait for them here
-__device__ __forceinline__ bool wait_quant(const EncodeParams &p, WorkDesc &d) {
+__device__ __forceinline__ bool wait_quant(const EncodeParams &p, WorkDesc &d, int lane) {
     const uint64_t *w = p.fq + ((int64_t)d.f * 3 + d.comp) * 2;
     uint64_t w0 = ld_relaxed_u64(w), w1 = ld_relaxed_u64(w + 1);
     SpinClock clk;
+    if (p.stats && lane == 0 && !(w0 & w1 & kFqValid)) atomicAdd(p.stats + 30, 1ull);  // (statistics build only)
     while (!(w0 & w1 & kFqValid)) {
         __nanosleep(100);
+        if (p.stats && lane == 0) atomicAdd(p.stats + 31, 1ull);
         if (spin_expired(clk)) { spin_timeout(p.error, 1, d.blk); return false; }
         w0 = ld_relaxed_u64(w);
         w1 = ld_relaxed_u64(w + 1);
@@ -85,19 +87,9 @@ __device__ __forceinline__ int arena_alloc(ParkFifo &ff, int need, int &span) {
 // write all 32 x width words of a block -- a multiple of four -- and the residuals
 // beyond a ragged block's length are zero, so the words past the block's last one
 // are there and zero; four words starting at a multiple of four share a skew row.
-__device__ __forceinline__ uint4 arena_chunk(const uint32_t *src, int c, int nWords) {
-#if MNW_EXP & 2
+__device__ __forceinline__ uint4 arena_chunk(const uint32_t *src, int c) {
     const uint32_t *w = src + skew(c * 4);
     return make_uint4(w[0], w[1], w[2], w[3]);
-#else
-    const int m = c * 4;
-    uint4 o;
-    o.x = src[skew(m)];
-    o.y = m + 1 < nWords ? src[skew(m + 1)] : 0u;
-    o.z = m + 2 < nWords ? src[skew(m + 2)] : 0u;
-    o.w = m + 3 < nWords ? src[skew(m + 3)] : 0u;
-    return o;
-#endif
 }
 
 // the oldest block that still sits in the arena moves to its record's scratch slot
@@ -107,7 +99,7 @@ __device__ __forceinline__ void spill_oldest_resident(ParkFifo &ff, int lane) {
     uint4 *slot = reinterpret_cast<uint4 *>(ff.slots + (size_t)k * kSlotWords);
     const uint32_t *src = ff.arena + wh.x;
 #pragma unroll 1
-    for (int c = lane; c < wh.w; c += 32) slot[c] = arena_chunk(src, c, wh.z);
+    for (int c = lane; c < wh.w; c += 32) slot[c] = arena_chunk(src, c);
     __syncwarp();
     if (lane == 0) ff.where[k] = make_int4(-1, 0, wh.z, wh.w);
     ff.aUsed -= wh.y;
@@ -131,7 +123,7 @@ __device__ __forceinline__ void place_finish(const EncodeParams &p, ParkFifo &ff
         if (wh.x >= 0) {
             const uint32_t *src = ff.arena + wh.x;
 #pragma unroll 1
-            for (int c = lane; c < size16; c += 32) st_stream_u4(dst + c, arena_chunk(src, c, wh.z));
+            for (int c = lane; c < size16; c += 32) st_stream_u4(dst + c, arena_chunk(src, c));
         } else {
             const uint4 *slot = reinterpret_cast<const uint4 *>(ff.slots + (size_t)k * kSlotWords);
 #pragma unroll 1
@@ -208,7 +200,8 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
         // the lane's 32 values to registers, the stage back to the producer
         load_block32(stage, lane, q);
         release_stage(rc, s, (d.flags & kDescSlow) != 0, lane);
-        if (!(d.flags & kDescQuant) && !wait_quant(p, d)) return false;
+        if (kStats && p.stats && lane == 0 && !(d.flags & kDescQuant)) atomicAdd(p.stats + 29, 1ull);
+        if (!(d.flags & kDescQuant) && !wait_quant(p, d, lane)) return false;
     }
     const uint32_t top = (1u << d.depth) - 1u;
     const bool biased = d.depth <= 23;

@@ -117,15 +117,10 @@ template <bool kPos, bool kBiased>
 __device__ __forceinline__ void quantise32(const Unwrap &uw, float x0, double scale, uint32_t top,
                                            uint32_t (&q)[kChunk]) {
     const float topf = (float)top;
-#if MNW_EXP & 1
     if (kPos) unwrap32(uw, q);
-#endif
 #pragma unroll
     for (int i = 0; i < kChunk; i++) {
-        float u = __uint_as_float(q[i]);
-#if !(MNW_EXP & 1)
-        if (kPos) u = unwrap_t(u, uw);
-#endif
+        const float u = __uint_as_float(q[i]);
         const float a = __fsub_rn(u, x0);
 #if defined(MNW_ABLATE) && (MNW_ABLATE & 1)
         const float s = __fmul_rn(a, (float)scale);  // timing experiment only: not the exact quotient

@@ -243,6 +243,10 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
                 100.0 * h[0] / tot, 100.0 * h[1] / tot, 100.0 * h[4] / tot, (double)h[0] / (double)(h[5] ? h[5] : 1),
                 (double)h[1] / (double)(h[6] ? h[6] : 1), h[5], h[6]);
         const double nB = (double)(h[6] ? h[6] : 1);
+        fprintf(stderr, "[mnwcuda encode stats] B blocks planned before their parameters were published (the consumer fetches them): %.1f%%\n",
+                100.0 * (double)h[29] / nB);
+        fprintf(stderr, "[mnwcuda encode stats] ... of which not published when the consumer looked either: %.1f%% of all B blocks, %.1f polls each\n",
+                100.0 * (double)h[30] / nB, (double)h[31] / (double)(h[30] ? h[30] : 1));
         fprintf(stderr, "[mnwcuda encode stats] clk/B-block by phase: params %.0f quantise %.0f delta+width %.0f pack %.0f "
                         "wait-free-record %.0f park+place %.0f | through scratch slots %.1f%% | queue time spent on A blocks %.1f%%\n",
                 h[8] / nB, h[9] / nB, h[10] / nB, h[11] / nB, h[12] / nB, h[13] / nB, 100.0 * h[15] / nB,
