@@ -187,7 +187,7 @@ __device__ __forceinline__ void planner(const EncodeParams &p, const CUtensorMap
             if (blk < p.nBlocks) d.kind = kWorkA;
         } else {
             blk = (g - p.lagG) * kGroupBlocks + (lane - kGroupBlocks);
-            if (blk >= 0 && blk < p.nBlocks) d.kind = kWorkB;
+            if (blk >= 0 && blk < p.nBlocks && !(p.dbg & 64)) d.kind = kWorkB;  // (64: A work alone, timing experiment)
         }
         d.blk = blk;
         if (d.kind == kWorkA || d.kind == kWorkB) {

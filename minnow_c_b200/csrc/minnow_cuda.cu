@@ -523,13 +523,20 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     const int64_t fieldGroups = (pl.maxBlocksPerField + kGroupBlocks - 1) / kGroupBlocks;
     p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + ctx->encodeMargin;
     if (p.lagG < fieldGroups + 1) p.lagG = fieldGroups + 1;
+    // timing experiments (scripts/enc_only.py; the output of such a call is not a valid stream):
+    // "B" = B work alone with the parameters the previous call on this batch left in ctx->quant,
+    // "A" = A work alone (MNWCUDA_DBG 64 makes the planner skip the B slots and the scan warp leave)
+    const char *only = getenv("MNWCUDA_ENCODE_ONLY");
+    const bool onlyB = only && only[0] == 'B';
+    if (onlyB) p.lagG = -1;
     mark(ctx, 0, s);
     if (pl.hasEmpty) {
         k_depth_empty<<<(unsigned)((nFields + 127) / 128), 128, 0, s>>>(p);
         ctx->launches++;
     }
     if (pl.nBlocks > 0) {
-        p.nGroups = (pl.nBlocks + kGroupBlocks - 1) / kGroupBlocks + p.lagG;
+        p.nGroups = onlyB ? (pl.nBlocks + kGroupSlots - 1) / kGroupSlots
+                          : (pl.nBlocks + kGroupBlocks - 1) / kGroupBlocks + p.lagG;
         if (p.nGroups >= (1ll << 31) - 1) return -5;
         launch_encode(ctx, p, pl.floatEnd, false, s);
     }
