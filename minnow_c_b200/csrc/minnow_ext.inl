@@ -645,6 +645,7 @@ int block_params(MnwCudaCtx *ctx, const uint8_t *d_stream, const uint64_t *d_off
     p.offsets = d_offsets;
     p.fields = static_cast<DevField *>(ctx->fields.need((size_t)nFields * sizeof(DevField)));
     p.nFields = (int)nFields;
+    p.uniformTasks = pl.uniformBlocks;  // k_block_headers reads it as blocks per field (0: fields differ)
     p.error = ctx->error;
     CUDA_CHECK(cudaMemcpyAsync(const_cast<DevField *>(p.fields), pl.fields.data(), (size_t)nFields * sizeof(DevField),
                                cudaMemcpyHostToDevice, s));
@@ -665,7 +666,7 @@ extern "C" int mnwcuda_BlockHeadersDev(MnwCudaCtx *ctx, const uint8_t *d_stream,
     int rc = block_params(ctx, d_stream, d_offsets, h_fields, nFields, p, nEntries, s);
     if (rc) return rc;
     mark(ctx, 3, s);
-    k_block_headers<<<(unsigned)((nEntries + 127) / 128), 128, 0, s>>>(
+    k_block_headers<<<(unsigned)(nFields + (nEntries - nFields + 127) / 128), 128, 0, s>>>(
         p, reinterpret_cast<MnwBlockHeaderDev *>(d_headers), 0, nullptr, nEntries);
     mark(ctx, 4, s);
     ctx->launches++;
@@ -688,8 +689,8 @@ extern "C" int mnwcuda_VerifyBlocksDev(MnwCudaCtx *ctx, uint8_t *d_stream, const
     std::vector<int32_t> ones((size_t)nFields, 1);
     CUDA_CHECK(cudaMemcpyAsync(d_fieldValid, ones.data(), (size_t)nFields * 4, cudaMemcpyHostToDevice, s));
     const unsigned grid = (unsigned)((nEntries + 127) / 128);
-    k_block_headers<<<grid, 128, 0, s>>>(p, reinterpret_cast<MnwBlockHeaderDev *>(const_cast<MnwBlockHeader *>(d_headers)),
-                                         1, d_damaged, nEntries);
+    k_block_headers<<<(unsigned)(nFields + (nEntries - nFields + 127) / 128), 128, 0, s>>>(
+        p, reinterpret_cast<MnwBlockHeaderDev *>(const_cast<MnwBlockHeader *>(d_headers)), 1, d_damaged, nEntries);
     k_mark_damage<<<grid, 128, 0, s>>>(p, d_damaged, d_fieldValid, nEntries);
     ctx->launches += 2;
     CUDA_CHECK(cudaGetLastError());

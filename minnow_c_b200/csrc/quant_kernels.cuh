@@ -250,26 +250,63 @@ __global__ void __launch_bounds__(256) k_u_restore(const uint64_t *q, int32_t n,
 __device__ __forceinline__ uint32_t checksum_word(uint32_t c, uint32_t w) {
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        c = __funnelshift_r(c, c, 1) + ((w >> (8 * k)) & 0xffu);
+        // rotate right by one = the high word of (c:c) << 31; with the addition it is
+        // one funnel-shift-and-add (LEA.HI) per byte on the dependent chain
+        c = __funnelshift_l(c, c, 31) + ((w >> (8 * k)) & 0xffu);
     }
     return c;
 }
+// The same with the byte picked and added by a dot product (IDP.4A on the FMA pipe): two
+// dependent instructions per byte instead of one, but one ALU-pipe instruction per byte
+// instead of 2.5 -- for the many short chains of the packed blocks, which are bound by the
+// ALU pipe's throughput, not by the chain's latency.
+__device__ __forceinline__ uint32_t checksum_word_dp(uint32_t c, uint32_t w) {
+    c = __dp4a(w, 0x00000001u, __funnelshift_l(c, c, 31));
+    c = __dp4a(w, 0x00000100u, __funnelshift_l(c, c, 31));
+    c = __dp4a(w, 0x00010000u, __funnelshift_l(c, c, 31));
+    return __dp4a(w, 0x01000000u, __funnelshift_l(c, c, 31));
+}
+template <bool kShort>
+__device__ __forceinline__ uint32_t checksum_16(uint32_t c, const uint4 &a) {
+    if (kShort) {
+        c = checksum_word_dp(c, a.x);
+        c = checksum_word_dp(c, a.y);
+        c = checksum_word_dp(c, a.z);
+        return checksum_word_dp(c, a.w);
+    }
+    c = checksum_word(c, a.x);
+    c = checksum_word(c, a.y);
+    c = checksum_word(c, a.z);
+    return checksum_word(c, a.w);
+}
+constexpr int kSumAhead = 8;  // 16-byte loads in flight per thread: a range is one dependent chain, so the
+                              // next 128 bytes are asked for before the current ones are summed
+template <bool kShort = false>
 __device__ __forceinline__ uint32_t checksum_range(const uint8_t *src, int64_t len) {
     uint32_t c = 1;
     int64_t i = 0;
     if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
         const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
-        for (; i + 32 <= len; i += 32) {  // a whole 32-byte sector per trip
-            const uint4 a = ld_stream_u4(s4 + (i >> 4)), b = ld_stream_u4(s4 + (i >> 4) + 1);
-            c = checksum_word(c, a.x); c = checksum_word(c, a.y); c = checksum_word(c, a.z); c = checksum_word(c, a.w);
-            c = checksum_word(c, b.x); c = checksum_word(c, b.y); c = checksum_word(c, b.z); c = checksum_word(c, b.w);
+        const int64_t groups = len / (16 * kSumAhead);
+        uint4 cur[kSumAhead], nxt[kSumAhead];
+        if (groups > 0) {
+#pragma unroll
+            for (int k = 0; k < kSumAhead; k++) cur[k] = ld_stream_u4(s4 + k);
         }
-        for (; i + 16 <= len; i += 16) {
-            const uint4 a = ld_stream_u4(s4 + (i >> 4));
-            c = checksum_word(c, a.x); c = checksum_word(c, a.y); c = checksum_word(c, a.z); c = checksum_word(c, a.w);
+        for (int64_t g = 0; g < groups; g++) {
+            if (g + 1 < groups) {
+#pragma unroll
+                for (int k = 0; k < kSumAhead; k++) nxt[k] = ld_stream_u4(s4 + (g + 1) * kSumAhead + k);
+            }
+#pragma unroll
+            for (int k = 0; k < kSumAhead; k++) c = checksum_16<kShort>(c, cur[k]);
+#pragma unroll
+            for (int k = 0; k < kSumAhead; k++) cur[k] = nxt[k];
         }
+        i = groups * 16 * kSumAhead;
+        for (; i + 16 <= len; i += 16) c = checksum_16<kShort>(c, ld_stream_u4(s4 + (i >> 4)));
     }
-    for (; i < len; i++) c = __funnelshift_r(c, c, 1) + src[i];
+    for (; i < len; i++) c = __funnelshift_l(c, c, 31) + src[i];
     return c;
 }
 
@@ -293,29 +330,81 @@ struct MnwBlockHeaderDev {
     int32_t Length;
     uint32_t Checksum;
 };
+// A field's block 0 (header + table: 48 bytes per block of the field, 192 KiB for 2^22
+// particles) is one long chain. One CTA per field: threads 1..127 stream the range into a
+// double-buffered staging area in shared memory with coalesced loads, thread 0 runs the
+// chain out of it -- one LEA.HI per byte, never waiting for DRAM.
+constexpr int kB0Chunk16 = 512;  // 16-byte words per staging buffer (8 KiB)
+
+__device__ __forceinline__ uint32_t checksum_block0(const uint8_t *src, int64_t len, uint4 (*buf)[kB0Chunk16]) {
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    const int64_t n16 = len >> 4;  // len = 64 + 48 nb: a multiple of 16
+    const int64_t chunks = (n16 + kB0Chunk16 - 1) / kB0Chunk16;
+    uint32_t c = 1;
+    auto fill = [&](int64_t ch) {
+        if (threadIdx.x == 0) return;
+        const int64_t base = ch * kB0Chunk16;
+        const int cnt = (int)min((int64_t)kB0Chunk16, n16 - base);
+        for (int i = (int)threadIdx.x - 1; i < cnt; i += (int)blockDim.x - 1) buf[ch & 1][i] = ld_stream_u4(s4 + base + i);
+    };
+    fill(0);
+    __syncthreads();
+    for (int64_t ch = 0; ch < chunks; ch++) {
+        if (ch + 1 < chunks) fill(ch + 1);
+        if (threadIdx.x == 0) {
+            const int cnt = (int)min((int64_t)kB0Chunk16, n16 - ch * kB0Chunk16);
+            const uint4 *b = buf[ch & 1];
+#pragma unroll 4
+            for (int i = 0; i < cnt; i++) c = checksum_16<false>(c, b[i]);
+        }
+        __syncthreads();
+    }
+    return c;
+}
+
+// Grid: one CTA per field for its block 0, then one thread per packed block. e is the
+// entry's index in the BlockHeader table.
 __global__ void __launch_bounds__(128) k_block_headers(DecodeParams p, MnwBlockHeaderDev *headers, int verify,
                                                        uint8_t *damaged, int64_t nEntries) {
-    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= nEntries) return;
+    __shared__ uint4 buf[2][kB0Chunk16];
     const DevField *fields = p.fields;
-    const int f = find_field(p.nFields, e, [fields](int i) { return fields[i].firstBlock + i; });
+    int f;
+    int64_t k;
+    if ((int64_t)blockIdx.x < p.nFields) {
+        f = (int)blockIdx.x;
+        k = 0;
+    } else {
+        const int64_t d = ((int64_t)blockIdx.x - p.nFields) * blockDim.x + threadIdx.x;  // packed block d of the batch
+        if (d >= nEntries - p.nFields) return;
+        // (p.uniformTasks is the blocks per field here when all fields have as many: no search --
+        // nine dependent loads -- in front of every thread's work)
+        if (p.uniformTasks > 0) f = (int)(d / p.uniformTasks);
+        else f = find_field(p.nFields, d, [fields](int i) { return fields[i].firstBlock; });
+        k = d - fields[f].firstBlock + 1;
+    }
     const DevField fd = p.fields[f];
-    const int64_t k = e - (fd.firstBlock + f);
+    const int64_t e = fd.firstBlock + f + k;
     const uint8_t *region = p.in + p.offsets[f];
     const int64_t regionLen = (int64_t)(p.offsets[f + 1] - p.offsets[f]);
     const int64_t fixed = 64 + (int64_t)fd.nb * 48;
     int64_t at = 0, len = fixed;
     bool inside = (p.offsets[f] & 15u) == 0 && regionLen >= fixed;
-    if (k > 0 && inside) {
-        const uint4 ent = __ldg(reinterpret_cast<const uint4 *>(region + 64) + (k - 1));
-        const int b = (int)((k - 1) % fd.nb);
-        const int cnt = min(kBlockLen, fd.n - b * kBlockLen);
-        const uint32_t w = ent.z > (uint32_t)kMaxWidth ? 0u : ent.z;
-        at = fixed + (int64_t)ent.w * 16;
-        len = (int64_t)((((cnt * (int)w + 31) >> 5) + 3) >> 2) * 16;
-        inside = ent.z <= (uint32_t)kMaxWidth && at + len <= regionLen;
+    uint32_t sum = 0u;
+    if (k == 0) {  // (uniform over the CTA)
+        if (inside) sum = checksum_block0(region, len, buf);
+        if (threadIdx.x != 0) return;
+    } else {
+        if (inside) {
+            const uint4 ent = __ldg(reinterpret_cast<const uint4 *>(region + 64) + (k - 1));
+            const int b = (int)((k - 1) % fd.nb);
+            const int cnt = min(kBlockLen, fd.n - b * kBlockLen);
+            const uint32_t w = ent.z > (uint32_t)kMaxWidth ? 0u : ent.z;
+            at = fixed + (int64_t)ent.w * 16;
+            len = (int64_t)((((cnt * (int)w + 31) >> 5) + 3) >> 2) * 16;
+            inside = ent.z <= (uint32_t)kMaxWidth && at + len <= regionLen;
+        }
+        if (inside) sum = checksum_range<true>(region + at, len);
     }
-    const uint32_t sum = inside ? checksum_range(region + at, len) : 0u;
     if (!verify) {
         headers[e].Length = (int32_t)len;
         headers[e].Checksum = sum;
