@@ -226,13 +226,9 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
         uw.tHi = d.tHi;
         uw.tLo = d.tLo;
         uw.L = d.L;
-        if (d.flags & kDescPos) {
-            if (biased) quantise32<true, true>(uw, d.x0, d.scale, top, q);
-            else quantise32<true, false>(uw, d.x0, d.scale, top, q);
-        } else {
-            if (biased) quantise32<false, true>(uw, d.x0, d.scale, top, q);
-            else quantise32<false, false>(uw, d.x0, d.scale, top, q);
-        }
+        if (d.flags & kDescPos) unwrap32(uw, q);
+        if (biased) quantise32<true>(d.x0, d.scale, top, q);
+        else quantise32<false>(d.x0, d.scale, top, q);
     }
 
     MNW_PHASE(1)

@@ -113,11 +113,12 @@ __device__ __forceinline__ void unwrap32(const Unwrap &uw, uint32_t (&q)[kChunk]
 }
 
 // in place: q holds the raw floats' bit patterns on entry, the indices on return
-template <bool kPos, bool kBiased>
-__device__ __forceinline__ void quantise32(const Unwrap &uw, float x0, double scale, uint32_t top,
-                                           uint32_t (&q)[kChunk]) {
+// (One body for positions and velocities -- the unwrap is a pass of its own, unwrap32 --
+// so that the consumers of an SM, which work on both kinds at once, share its code: the
+// kernel is sensitive to the size of the code its warps are spread over.)
+template <bool kBiased>
+__device__ __forceinline__ void quantise32(float x0, double scale, uint32_t top, uint32_t (&q)[kChunk]) {
     const float topf = (float)top;
-    if (kPos) unwrap32(uw, q);
 #pragma unroll
     for (int i = 0; i < kChunk; i++) {
         const float u = __uint_as_float(q[i]);
