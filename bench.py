@@ -142,6 +142,22 @@ def generate(codec, d_in, ngrid, first_id, n_segments, seg=SEG, noise_cells=0.0)
 NOMINAL_HBM_GBS = 8000.0  # HBM3e as specified; the roofline's denominator is the measured copy bandwidth
 
 
+def native_so_loaded():
+    """In-tree shared objects mapped into this process (from /proc/self/maps)."""
+    seen = []
+    try:
+        with open("/proc/self/maps") as fh:
+            for ln in fh:
+                path = ln.rstrip("\n").split(None, 5)[-1] if len(ln.split(None, 5)) == 6 else ""
+                if path.endswith(".so") and os.path.realpath(path).startswith(os.path.realpath(ROOT) + os.sep):
+                    rel = os.path.relpath(os.path.realpath(path), os.path.realpath(ROOT))
+                    if rel not in seen:
+                        seen.append(rel)
+    except OSError:
+        pass
+    return sorted(seen)
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -257,6 +273,8 @@ def run_reference(args):
         "cpu_baseline": base,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": wall,
+        # what this process mapped from the repository: the oracle's libraries, nothing of the product
+        "native_so_loaded": native_so_loaded(),
     }
     print(json.dumps(line), flush=True)
     return 0
@@ -477,6 +495,7 @@ def run_b200(args):
         "encode_ms": enc_ms / args.steps, "decode_ms": dec_ms / args.steps,
         "kernel_ms": {k: round(v, 4) for k, v in kt.items()},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+        "native_so_loaded": native_so_loaded(),
         "clocks": clk, "check": check, "wall_s": t_wall,
     }
     if gather is not None:
