@@ -110,12 +110,17 @@ def test_uint_fields_match_oracle(codec, orc, n):
     assert np.array_equal(codec.decode_ints(mc.FIELD_UNSI, n, payload), data)
 
 
-def test_block_headers_of_a_batch_match_oracle(codec):
+@pytest.mark.parametrize("grid,sizes", [(32, [4096, 5000, 1, 8192]),
+                                        # a field whose block 0 (header + table, 28 KB) spans several staging
+                                        # chunks of the per-field CTA, an empty field, fields of unequal size
+                                        (96, [600000, 0, 3000, 70000]),
+                                        (64, [65536, 65536, 65536])],  # equal sizes: no field search
+                         ids=["small", "long_table_and_empty", "uniform"])
+def test_block_headers_of_a_batch_match_oracle(codec, grid, sizes):
     """mnwcuda_BlockHeadersDev on the device-resident stream of a batch: every
     block's {Length, Checksum} equals the oracle's segment image table"""
     orc = _oracle.port()
-    pos, vel = zeldovich_host(32)
-    sizes = [4096, 5000, 1, 8192]
+    pos, vel = zeldovich_host(grid)
     fields, chunks, off, start = [], [], 0, 0
     for i, n in enumerate(sizes):
         src, code, delta, width = (pos, mc.FIELD_POSN, 1e-3, 100.0) if i % 2 == 0 else (vel, mc.FIELD_VELC, 0.5, 0.0)
