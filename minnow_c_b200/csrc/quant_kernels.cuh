@@ -334,7 +334,7 @@ struct MnwBlockHeaderDev {
 // particles) is one long chain. One CTA per field: threads 1..127 stream the range into a
 // double-buffered staging area in shared memory with coalesced loads, thread 0 runs the
 // chain out of it -- one LEA.HI per byte, never waiting for DRAM.
-constexpr int kB0Chunk16 = 512;  // 16-byte words per staging buffer (8 KiB)
+constexpr int kB0Chunk16 = 640;  // 16-byte words per staging buffer (10 KiB)
 
 __device__ __forceinline__ uint32_t checksum_block0(const uint8_t *src, int64_t len, uint4 (*buf)[kB0Chunk16]) {
     const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
@@ -362,20 +362,57 @@ __device__ __forceinline__ uint32_t checksum_block0(const uint8_t *src, int64_t 
     return c;
 }
 
+// Packed blocks, one per thread: a thread reading its own block 16 bytes at a time
+// touches 32 different lines per warp-wide load, and the L1 queue becomes the limit.
+// Instead the warp fetches everybody's next 128 bytes together -- a quarter warp per
+// thread's piece, 4 x 128 contiguous bytes per load instruction -- into shared memory, and
+// every lane then sums its own piece from there. Lengths are multiples of 16, pointers
+// 16-byte aligned (a lane with nothing to do passes len 0).
+constexpr int kSumPiece16 = 8;           // 16-byte words per lane and round
+constexpr int kSumRow = kSumPiece16 + 1;  // row stride in shared memory (odd: the lanes' rows spread over the banks)
+
+__device__ __forceinline__ uint32_t checksum_blocks32(const uint8_t *src, int64_t len, uint4 (*st)[kSumRow]) {
+    const int lane = threadIdx.x & 31;
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    int rem = (int)(len >> 4);  // 16-byte words left
+    uint32_t c = 1;
+    while (__any_sync(kFull, rem > 0)) {
+#pragma unroll
+        for (int i = 0; i < 32 / 4; i++) {
+            const int j = 4 * i + (lane >> 3);  // the lane whose piece this quarter warp fetches
+            const uint64_t pj = __shfl_sync(kFull, (uint64_t)(uintptr_t)s4, j);
+            const int rj = __shfl_sync(kFull, rem, j);
+            const int w = lane & 7;
+            if (w < rj) st[j][w] = ld_stream_u4(reinterpret_cast<const uint4 *>((uintptr_t)pj) + w);
+        }
+        __syncwarp();
+        const int n = min(rem, kSumPiece16);
+        for (int w = 0; w < n; w++) c = checksum_16<true>(c, st[lane][w]);
+        s4 += n;
+        rem -= n;
+        __syncwarp();
+    }
+    return c;
+}
+
 // Grid: one CTA per field for its block 0, then one thread per packed block. e is the
 // entry's index in the BlockHeader table.
 __global__ void __launch_bounds__(128) k_block_headers(DecodeParams p, MnwBlockHeaderDev *headers, int verify,
                                                        uint8_t *damaged, int64_t nEntries) {
-    __shared__ uint4 buf[2][kB0Chunk16];
+    __shared__ uint4 buf[2][kB0Chunk16];  // block 0 CTAs (checksum_block0) ...
+    uint4 (*stageSum)[32][kSumRow] = reinterpret_cast<uint4 (*)[32][kSumRow]>(&buf[0][0]);  // ... or the others
+    static_assert(sizeof(buf) >= 4 * 32 * kSumRow * sizeof(uint4), "k_block_headers: staging area of four warps");
     const DevField *fields = p.fields;
     int f;
     int64_t k;
+    bool live = true;
     if ((int64_t)blockIdx.x < p.nFields) {
         f = (int)blockIdx.x;
         k = 0;
     } else {
-        const int64_t d = ((int64_t)blockIdx.x - p.nFields) * blockDim.x + threadIdx.x;  // packed block d of the batch
-        if (d >= nEntries - p.nFields) return;
+        int64_t d = ((int64_t)blockIdx.x - p.nFields) * blockDim.x + threadIdx.x;  // packed block d of the batch
+        live = d < nEntries - p.nFields;  // (a dead thread stays for the warp's shuffles, on block 0 of the batch)
+        if (!live) d = 0;
         // (p.uniformTasks is the blocks per field here when all fields have as many: no search --
         // nine dependent loads -- in front of every thread's work)
         if (p.uniformTasks > 0) f = (int)(d / p.uniformTasks);
@@ -394,6 +431,7 @@ __global__ void __launch_bounds__(128) k_block_headers(DecodeParams p, MnwBlockH
         if (inside) sum = checksum_block0(region, len, buf);
         if (threadIdx.x != 0) return;
     } else {
+        inside = inside && live;
         if (inside) {
             const uint4 ent = __ldg(reinterpret_cast<const uint4 *>(region + 64) + (k - 1));
             const int b = (int)((k - 1) % fd.nb);
@@ -403,8 +441,10 @@ __global__ void __launch_bounds__(128) k_block_headers(DecodeParams p, MnwBlockH
             len = (int64_t)((((cnt * (int)w + 31) >> 5) + 3) >> 2) * 16;
             inside = ent.z <= (uint32_t)kMaxWidth && at + len <= regionLen;
         }
-        if (inside) sum = checksum_range<true>(region + at, len);
+        // the packed blocks of a warp's 32 threads are summed together, staged through shared memory
+        sum = checksum_blocks32(inside ? region + at : nullptr, inside ? len : 0, stageSum[threadIdx.x >> 5]);
     }
+    if (!live) return;
     if (!verify) {
         headers[e].Length = (int32_t)len;
         headers[e].Checksum = sum;
