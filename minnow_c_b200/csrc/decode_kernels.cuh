@@ -19,7 +19,7 @@ struct DecodeParams {
     DevQuant *quant;   // [nFields] parsed from the headers
     uint64_t *seeds;   // [nFields]
     int *tableOf;      // [nFields] field whose stream table this field uses
-    uint64_t *states;  // [nFields][maxStreams][2]
+    uint64_t *states;  // [nFields][maxStreams][2], or [maxStreams][nFields][2] when statesByStream
     int64_t maxStreams;
     const uint64_t *jumpPow;  // [kJumpPows][128][2]: columns of J^(2^k)
     float *out;
@@ -27,7 +27,12 @@ struct DecodeParams {
     int *error;
     uint32_t *dmgCount;  // tasks that hold a damaged block (k_damaged_tasks blanks those blocks afterwards)
     uint32_t *dmgList;   // [nTasks]
+    int statesByStream;  // k_stream_states_tab writes stream-major: a CTA's states of one k for all fields are contiguous
 };
+
+__device__ __forceinline__ int64_t state_index(const DecodeParams &p, int f, int64_t k) {
+    return p.statesByStream ? k * p.nFields + f : (int64_t)f * p.maxStreams + k;
+}
 
 constexpr int kJumpPows = 26;
 constexpr uint32_t kWidthDamaged = 0xffffffffu;  // table entry of a block whose checksum failed (k_block_headers)
@@ -132,7 +137,7 @@ __global__ void __launch_bounds__(128) k_stream_states(DecodeParams p) {
         s0 = a;
         s1 = b;
     }
-    uint64_t *dst = p.states + ((int64_t)f * p.maxStreams + k) * 2;
+    uint64_t *dst = p.states + state_index(p, f, k) * 2;
     dst[0] = s0;
     dst[1] = s1;
 }
@@ -172,22 +177,46 @@ __global__ void __launch_bounds__(128) k_jump_table(const uint64_t *jumpPow, ulo
     tab[k * 128 + i] = make_ulonglong2(s0, s1);
 }
 
+// The CTA first turns the 128 columns of its J^k into a table of nibble products
+// (32 nibbles x 16 values, 8 KiB of shared memory: entry [n][v] = XOR of the columns
+// 4n + b over the set bits b of v), so that a matrix-vector product is 32 look-ups
+// and XORs (~230 instructions) instead of 128 masked columns (~1000).
 __global__ void __launch_bounds__(128) k_stream_states_tab(DecodeParams p, const ulonglong2 *tab) {
     __shared__ ulonglong2 col[128];
+    __shared__ ulonglong2 nib[32][16];
     const int64_t k = blockIdx.x;
     col[threadIdx.x] = tab[k * 128 + threadIdx.x];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int e = threadIdx.x * 4 + j, n = e >> 4, v = e & 15;
+        ulonglong2 x = make_ulonglong2(0ull, 0ull);
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+            if ((v >> b) & 1) {
+                x.x ^= col[4 * n + b].x;
+                x.y ^= col[4 * n + b].y;
+            }
+        nib[n][v] = x;
+    }
     __syncthreads();
     for (int f = threadIdx.x; f < p.nFields; f += blockDim.x) {
         if (p.tableOf[f] != f) continue;
         const int64_t nStreams = (3 * (int64_t)p.fields[f].nb + kRun - 1) / kRun * 32;
         if (k >= nStreams) continue;
         uint64_t sm = p.seeds[f];
-        uint64_t s0 = splitmix_next(sm);
-        uint64_t s1 = splitmix_next(sm);
-        gf2_matvec(col, s0, s1);
-        uint64_t *dst = p.states + ((int64_t)f * p.maxStreams + k) * 2;
-        dst[0] = s0;
-        dst[1] = s1;
+        const uint64_t s0 = splitmix_next(sm);
+        const uint64_t s1 = splitmix_next(sm);
+        uint64_t a = 0, b = 0;
+#pragma unroll
+        for (int n = 0; n < 16; n++) {
+            const ulonglong2 e0 = nib[n][(s0 >> (4 * n)) & 15u], e1 = nib[16 + n][(s1 >> (4 * n)) & 15u];
+            a ^= e0.x ^ e1.x;
+            b ^= e0.y ^ e1.y;
+        }
+        uint64_t *dst = p.states + state_index(p, f, k) * 2;
+        dst[0] = a;
+        dst[1] = b;
     }
 }
 
@@ -284,7 +313,7 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
     uint64_t s0 = 0, s1 = 0;
     if (!kToQ) {
         const uint64_t *sp =
-            p.states + ((int64_t)p.tableOf[f] * p.maxStreams + (int64_t)localTask * 32 + lane) * 2;
+            p.states + state_index(p, p.tableOf[f], (int64_t)localTask * 32 + lane) * 2;
         s0 = sp[0];
         s1 = sp[1];
     }

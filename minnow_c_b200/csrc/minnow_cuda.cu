@@ -595,6 +595,7 @@ extern "C" int mnwcuda_DecodeFieldsDev(MnwCudaCtx *ctx, const uint8_t *d_in, con
                 ctx->launches++;
             }
             CUDA_CHECK(cudaStreamWaitEvent(s, ctx->tabEv, 0));
+            p.statesByStream = 1;  // (a CTA writes its k's states of all fields as one contiguous run)
             k_stream_states_tab<<<(unsigned)pl.maxStreams, 128, 0, s>>>(p, static_cast<const ulonglong2 *>(ctx->jumpTab.ptr));
         } else {
             dim3 grid((unsigned)((pl.maxStreams + 127) / 128), (unsigned)nFields);
