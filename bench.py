@@ -476,8 +476,9 @@ def run_b200(args):
         check["sample_bytes_vs_reference"] = shard_parity
         check["ok"] = bool(check["ok"] and shard_parity["ok"])
 
-    checksums = refflow = None
+    checksums = refflow = halves = None
     if n_gpus == 1 and not args.no_sweep:
+        halves = run_encode_halves(torch, codec, d_in, descs, nf, d_out, d_off, alg_bytes, peak)
         checksums = run_checksums(torch, mc, codec, d_out, d_off, descs, nf, comp_bytes, peak)
         refflow = run_reference_flow(torch, mc, d_in, seg, fields)
     sweep = None
@@ -500,6 +501,8 @@ def run_b200(args):
     }
     if gather is not None:
         line["gather"] = gather
+    if halves is not None:
+        line["k_encode_halves"] = halves
     if checksums is not None:
         line["checksums"] = checksums
     if refflow is not None:
@@ -800,6 +803,48 @@ def run_sweep(torch, mc, codec, d_in, d_out, d_off, d_dec, fields, seg, peak, ng
     generate(codec, d_in, ngrid, first_id, n_seg, seg)  # back to the headline's field
     torch.cuda.synchronize()
     return out
+
+
+def run_encode_halves(torch, codec, d_in, descs, nf, d_out, d_off, alg_bytes, peak):
+    """k_encode's two halves on their own (explains the fused kernel's time; untimed in
+    the metric, and the output of these launches is not a valid stream): the B work
+    alone -- quantise .. pack .. place with the parameters the previous full launch left
+    behind, i.e. the one-pass encoder for callers that know the bounds, every read from
+    DRAM -- and the A work alone (the streaming min/max through the same ring)."""
+    codec.enable_kernel_timing(True)
+
+    def timed(reps=3):
+        ms = []
+        for _ in range(reps):
+            codec.encode_dev(d_in, descs, nf, d_out, d_off)
+            torch.cuda.synchronize()
+            ms.append(codec.kernel_times()["k_encode"])
+        return float(np.mean(ms))
+
+    fused = timed()
+    os.environ["MNWCUDA_ENCODE_ONLY"] = "B"
+    b_only = timed()
+    del os.environ["MNWCUDA_ENCODE_ONLY"]
+    old_dbg = os.environ.get("MNWCUDA_DBG")
+    os.environ["MNWCUDA_DBG"] = "64"
+    a_only = timed()
+    if old_dbg is None:
+        del os.environ["MNWCUDA_DBG"]
+    else:
+        os.environ["MNWCUDA_DBG"] = old_dbg
+    codec.status()  # (clears whatever the A-only launches raised: their output is never finalised properly)
+    codec.encode_dev(d_in, descs, nf, d_out, d_off)  # leave a valid stream behind for the legs that follow
+    torch.cuda.synchronize()
+    codec.enable_kernel_timing(False)
+    if codec.status() != 0:
+        raise SystemExit("device-side error after the encode-halves experiment")
+    raw = nf * 3 * SEG * 4
+    return {"fused_ms": round(fused, 4), "b_only_ms": round(b_only, 4), "a_only_ms": round(a_only, 4),
+            "b_only_frac": round(alg_bytes / (b_only * 1e-3) / 1e9 / peak, 4),
+            "a_only_read_gbs": round(raw / (a_only * 1e-3) / 1e9, 1),
+            "a_only_frac_of_peak": round(raw / (a_only * 1e-3) / 1e9 / peak, 4),
+            "note": "B only = the one-pass encoder with given quantisation parameters (MNWCUDA_ENCODE_ONLY=B), "
+                    "A only = min/max pass through the same TMA ring (MNWCUDA_DBG=64); timing experiments"}
 
 
 def run_checksums(torch, mc, codec, d_out, d_off, descs, nf, comp_bytes, peak):
