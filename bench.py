@@ -139,6 +139,7 @@ def generate(codec, d_in, ngrid, first_id, n_segments, seg=SEG, noise_cells=0.0)
         codec.generate(ngrid, BOX, GEN_SEED, first_id + s * seg, seg, pos, vel, noise_cells=noise_cells)
 
 
+P2P_COPY_CEILING_GBS = 774.5  # scripts/p2p_peak.py on a 4 x B200 box of this pool
 NOMINAL_HBM_GBS = 8000.0  # HBM3e as specified; the roofline's denominator is the measured copy bandwidth
 
 
@@ -548,6 +549,9 @@ def run_gather(torch, dist, shard, d_out, d_sizes, d_base, dev, rank):
     moved = total - sizes_h[0]
     gbs = moved / (float(ms.item()) * 1e-3) / 1e9
     return {"ms": float(ms.item()), "bytes_into_sink": moved, "gbs": gbs, "frac_of_900_gbs_ingress": gbs / 900.0,
+            # what plain device-to-device copies from 1..3 peers into one GPU reach on this pool's boxes
+            # (scripts/p2p_peak.py, measured once: 766 / 773 / 774.5 GB/s): the practical ingress ceiling
+            "p2p_copy_ceiling_gbs": P2P_COPY_CEILING_GBS, "frac_of_p2p_copy_ceiling": gbs / P2P_COPY_CEILING_GBS,
             "prefix_ok": bool(prefix_ok), "sink_slab_ok": same,
             "note": "mnwnccl_GatherStream: one ncclGroupStart..ncclSend/ncclRecv x ranks..ncclGroupEnd into rank 0; "
                     "not part of the metric"}
