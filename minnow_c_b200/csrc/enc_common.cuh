@@ -68,7 +68,11 @@ constexpr int kSlotWords = 832;      // scratch slot of one packed block: 25 bit
 constexpr uint32_t kAggReady = 0x8000u;       // in a 16-bit size word
 constexpr uint32_t kRelReady = 0x80000000u;   // in a 32-bit window-relative prefix
 constexpr uint64_t kPrefixReady = 1ull << 63; // in a 64-bit window base
-constexpr int kScanWin = 1024;                // blocks per scan window
+#ifndef MNW_SCAN_WIN
+#define MNW_SCAN_WIN 1024
+#endif
+constexpr int kScanWin = MNW_SCAN_WIN;        // blocks per scan window (a multiple of 256)
+constexpr int kScanRows = kScanWin / 256;     // 16-byte loads per lane and window
 constexpr int kRedWin = 512;                  // blocks per reduce window
 constexpr uint64_t kFqValid = 1ull << 63;
 constexpr uint32_t kQBias = 0x4b000000u;  // bit pattern of 2^23: trunc by add.rz keeps it in the exponent

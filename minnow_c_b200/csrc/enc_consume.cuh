@@ -245,9 +245,11 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
 
     // a record and room in the arena for this block (the pack routines write all
     // 32 x width words of a block, ragged or not)
+    if (kStats && p.stats && lane == 0 && ff.count == kFifo) atomicAdd(p.stats + 18, 1ull);  // all records taken
     if (ff.count == kFifo && !place_oldest(p, ff, lane)) return false;  // the only wait on another warp's work
     int span = 0, loc;
     while ((loc = arena_alloc(ff, 33 * bs.w + 1, span)) < 0) {
+        if (kStats && p.stats && lane == 0) atomicAdd(p.stats + 19, 1ull);  // the arena had no room
         const uint64_t pre = peek_prefix(p, ff.blk[ff.head]);
         if (pre) place_finish(p, ff, pre & ~kPrefixReady, lane);
         else spill_oldest_resident(ff, lane);

@@ -91,15 +91,15 @@ __global__ void k_depth_empty(EncodeParams p) {
 __device__ __forceinline__ bool agg_ready(const uint4 &v) {
     return (v.x & v.y & v.z & v.w & 0x80008000u) == 0x80008000u;
 }
-__device__ __forceinline__ void scan_load(const EncodeParams &p, int64_t base, int lane, uint4 (&a)[4]) {
+__device__ __forceinline__ void scan_load(const EncodeParams &p, int64_t base, int lane, uint4 (&a)[kScanRows]) {
 #pragma unroll
-    for (int j = 0; j < 4; j++) a[j] = ld_relaxed_u4(p.blkAgg + base + j * 256 + lane * 8);
+    for (int j = 0; j < kScanRows; j++) a[j] = ld_relaxed_u4(p.blkAgg + base + j * 256 + lane * 8);
 }
 
 __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
     if (p.dbg & 64) return;  // (A work alone, timing experiment: no block ever gets a size)
     uint64_t running = 0;
-    uint4 cur[4], nxt[4];
+    uint4 cur[kScanRows], nxt[kScanRows];
     scan_load(p, 0, lane, cur);
     int64_t w = 0;
     for (int64_t base = 0; base < p.nBlocks; base += kScanWin, w++) {
@@ -110,7 +110,7 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
         if (base + kScanWin > p.nBlocks) {
             // last, ragged window: blocks past the end count as there, with size 0
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < kScanRows; j++) {
                 uint32_t *wds = reinterpret_cast<uint32_t *>(&cur[j]);
 #pragma unroll
                 for (int i = 0; i < 8; i++)
@@ -121,7 +121,7 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
         while (true) {
             bool all = true;
 #pragma unroll
-            for (int j = 0; j < 4; j++) all = all && agg_ready(cur[j]);
+            for (int j = 0; j < kScanRows; j++) all = all && agg_ready(cur[j]);
             if (__all_sync(kFull, all)) {
                 if (p.stats && lane == 0) {  // MNWCUDA_ENCODE_STATS: was the window complete at first look?
                     p.stats[25] += 1;
@@ -135,7 +135,7 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
             }
             if (clk.spins > 16) __nanosleep(100);
 #pragma unroll
-            for (int j = 0; j < 4; j++)
+            for (int j = 0; j < kScanRows; j++)
                 if (!agg_ready(cur[j])) {
                     uint4 v = ld_relaxed_u4(p.blkAgg + base + j * 256 + lane * 8);
                     if (base + kScanWin > p.nBlocks) {
@@ -149,7 +149,7 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
         }
         uint32_t rowBase = 0;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < kScanRows; j++) {
             const uint32_t wd[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
             uint32_t sz[8];
 #pragma unroll
@@ -178,7 +178,7 @@ __device__ __forceinline__ void scan_blocks(const EncodeParams &p, int lane) {
         running += rowBase;
         if (more) {
 #pragma unroll
-            for (int j = 0; j < 4; j++) cur[j] = nxt[j];
+            for (int j = 0; j < kScanRows; j++) cur[j] = nxt[j];
         }
     }
     if (lane == 0)

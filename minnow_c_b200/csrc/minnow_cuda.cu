@@ -245,6 +245,8 @@ extern "C" void mnwcuda_Destroy(MnwCudaCtx *ctx) {
         const double nB = (double)(h[6] ? h[6] : 1);
         fprintf(stderr, "[mnwcuda encode stats] B blocks planned before their parameters were published (the consumer fetches them): %.1f%%\n",
                 100.0 * (double)h[29] / nB);
+        fprintf(stderr, "[mnwcuda encode stats] B blocks that found all of the consumer's records taken: %.1f%% | arena without room: %.2f times per block\n",
+                100.0 * (double)h[18] / nB, (double)h[19] / nB);
         fprintf(stderr, "[mnwcuda encode stats] ... of which not published when the consumer looked either: %.1f%% of all B blocks, %.1f polls each\n",
                 100.0 * (double)h[30] / nB, (double)h[31] / (double)(h[30] ? h[30] : 1));
         fprintf(stderr, "[mnwcuda encode stats] clk/B-block by phase: params %.0f quantise %.0f delta+width %.0f pack %.0f "

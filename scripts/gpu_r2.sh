@@ -19,11 +19,11 @@ except Exception as e:
 PY
 fi
 if [ -n "$STATS" ]; then
-  MNWCUDA_ENCODE_STATS=1 timeout 300 python bench.py --steps 3 --warmup 1 --no-cpu --no-e2e --no-sweep > /dev/null 2> gpurun_out/stats_${TAG}.err; grep "encode stats" gpurun_out/stats_${TAG}.err | tail -5
+  MNWCUDA_ENCODE_STATS=1 timeout 300 python bench.py --steps 3 --warmup 1 --no-cpu --no-e2e --no-sweep > /dev/null 2> gpurun_out/stats_${TAG}.err; grep "encode stats" gpurun_out/stats_${TAG}.err | tail -7
 fi
 if [ -n "$BENCH" ]; then
   timeout 1500 python bench.py > gpurun_out/bench_${TAG}.json 2> gpurun_out/bench_${TAG}.err; echo "bench exit $?"
-  head -c 6000 gpurun_out/bench_${TAG}.json; tail -5 gpurun_out/bench_${TAG}.err
+  head -c 6000 gpurun_out/bench_${TAG}.json; tail -7 gpurun_out/bench_${TAG}.err
 fi
 if [ -n "$REF" ]; then
   timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_${TAG}.json 2> gpurun_out/bench_ref_${TAG}.err; echo "ref exit $?"
