@@ -202,12 +202,16 @@ __device__ __forceinline__ void red_skip_empty(const EncodeParams &p, RedWalk &w
     if (w.f < p.nFields) w.compEnd = p.fields[w.f].firstBlock + p.fields[w.f].nb;
 }
 
+// kDefer: the field's parameters are not worked out here but by red_flush, 32 fields at
+// a time, one per lane (a batch of many small fields finishes hundreds of fields per window,
+// and compute_quant -- a division, the depth loop, dependent loads -- takes microseconds)
+template <bool kDefer = false>
 __device__ __forceinline__ void red_finish_comp(const EncodeParams &p, RedWalk &w, int lane) {
     if (lane == 0) {
         uint32_t *mm = p.minmax + ((int64_t)w.f * 3 + w.comp) * 2;
         mm[0] = w.lo;
         mm[1] = w.hi;
-        if (w.comp == 2) compute_quant(p, w.f);  // reads back what this thread has just written
+        if (!kDefer && w.comp == 2) compute_quant(p, w.f);  // reads back what this thread has just written
     }
     w.lo = w.hi = 0xffffffffu;
     if (++w.comp == 3) {
@@ -217,6 +221,17 @@ __device__ __forceinline__ void red_finish_comp(const EncodeParams &p, RedWalk &
     } else {
         w.compEnd += p.fields[w.f].nb;
     }
+}
+
+// the parameters of the fields [from, w.f) whose last component has been finished (kDefer)
+__device__ __forceinline__ void red_flush(const EncodeParams &p, const RedWalk &w, int &from, int lane) {
+    if (from >= w.f) return;
+    __syncwarp();  // lane 0's min/max words, for everybody
+    for (int f0 = from; f0 < w.f; f0 += 32) {
+        const int f = f0 + lane;
+        if (f < w.f && p.fields[f].nb > 0) compute_quant(p, f);  // (empty fields: k_depth_empty)
+    }
+    from = w.f;
 }
 
 __device__ __forceinline__ bool mm_ready(const uint4 &v) { return (v.x | v.y) != 0u && (v.z | v.w) != 0u; }
@@ -231,6 +246,7 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
     w.compEnd = 0;
     w.lo = w.hi = 0xffffffffu;
     red_skip_empty(p, w);
+    int pendFrom = w.f;  // first field whose parameters have not been worked out
     uint4 cur[8], nxt[8];
     red_load(p, 0, lane, cur);
     for (int64_t base = 0; base < p.nBlocks; base += kRedWin) {
@@ -278,7 +294,7 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
             }
             w.lo = min(w.lo, __reduce_min_sync(kFull, lo));
             w.hi = min(w.hi, __reduce_min_sync(kFull, hi));
-            if (base + kRedWin == w.compEnd) red_finish_comp(p, w, lane);
+            if (base + kRedWin == w.compEnd) red_finish_comp<true>(p, w, lane);
         } else {
             // component by component
             int64_t s0 = base;
@@ -300,9 +316,10 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
                 w.lo = min(w.lo, __reduce_min_sync(kFull, lo));
                 w.hi = min(w.hi, __reduce_min_sync(kFull, hi));
                 s0 = e;
-                if (s0 == w.compEnd) red_finish_comp(p, w, lane);
+                if (s0 == w.compEnd) red_finish_comp<true>(p, w, lane);
             }
         }
+        red_flush(p, w, pendFrom, lane);  // (w.f is the field in progress: everything before it is complete)
         if (more) {
 #pragma unroll
             for (int j = 0; j < 8; j++) cur[j] = nxt[j];
