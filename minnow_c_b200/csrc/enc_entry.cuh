@@ -12,7 +12,11 @@ namespace mnw {
 // kStats: the per-phase clocks of MNWCUDA_ENCODE_STATS; a separate instantiation so
 // that the normal kernel carries none of the clock reads and 64-bit adds (they were
 // a few per cent of the consumers' instructions).
-template <bool kFromQ, bool kStats>
+// kGeneral: the launch for big batches whose fields differ in size (the general parallel
+// reduce, enc_kernel.cuh) -- an instantiation of its own so that the kernel of the uniform
+// batches stays exactly what it is (its time moves with anything that changes its service
+// warps' code).
+template <bool kFromQ, bool kStats, bool kGeneral = false>
 __global__ void __launch_bounds__(kEncWarps * 32, 1)
 k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) uint8_t encSmem[];
@@ -39,8 +43,13 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     const bool service = gridDim.x >= 8 && blockIdx.x < 2;
     if (service && warp != kEncWarps - 1) {
         // CTA 1 of a big launch: its other warps reduce the windows in parallel
-        if (blockIdx.x == 1 && warp < kRedWarps && p.lagG >= 0 && !kFromQ && reduce_in_parallel(p))
-            reduce_windows(p, lane, warp);
+        if (blockIdx.x == 1 && p.lagG >= 0 && !kFromQ) {
+            if (kGeneral) {
+                if (warp < kRedWarpsGeneral) reduce_windows_general(p, lane, warp);
+            } else if (warp < kRedWarps && reduce_in_parallel(p)) {
+                reduce_windows(p, lane, warp);
+            }
+        }
         return;
     }
     // the last warp: scan in CTA 0, reduce in CTA 1, one more consumer everywhere else
@@ -56,7 +65,8 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     if (warp == kEncWarps - 1 && lastIsService) {
         if (blockIdx.x == 0) scan_blocks(p, lane);
         else if (p.lagG >= 0 && !kFromQ) {
-            if (gridDim.x >= 8 && reduce_in_parallel(p)) reduce_fold(p, lane);
+            if (kGeneral) reduce_fold_general(p, lane);  // (the host launches it with 8 CTAs or more only)
+            else if (gridDim.x >= 8 && reduce_in_parallel(p)) reduce_fold(p, lane);
             else reduce_fields(p, lane);
         }
         return;

@@ -201,6 +201,7 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -410,7 +411,7 @@ EncodeParams prepare_encode(MnwCudaCtx *ctx, const Plan &pl, uint8_t *d_out, int
     const size_t padRed = (size_t)((pl.nBlocks + kRedWin - 1) / kRedWin) * kRedWin;
     const size_t bWin = ((nWin + 1) * 8 + 15) & ~(size_t)15, bMM = padRed * 8, bFq = nF * 6 * 8;
     const size_t bRel = padScan * 4, bAgg = ((padScan * 2 + 15) & ~(size_t)15) + 16;
-    const size_t bWinMM = (padRed / kRedWin) * 8;
+    const size_t bWinMM = (padRed / kRedWin) * 32;  // 8 bytes per window (uniform batches) or a 32-byte record
     const size_t stateBytes = bWin + bMM + bFq + bRel + bAgg + bWinMM;
     p.tbl = static_cast<uint4 *>(ctx->misc.need((size_t)(pl.nBlocks + 1) * sizeof(uint4)));
     uint8_t *st = static_cast<uint8_t *>(ctx->tileState.need(stateBytes));
@@ -476,8 +477,13 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     // warp in CTA 1, ticket order), so all of them must be resident at once: a
     // cooperative launch starts the grid only when every CTA has an SM, whatever else
     // the device is running; the grid is sized by the occupancy query, never above it.
+    // big batches whose components are not whole reduce windows (fields of unequal size): the
+    // instantiation with the general parallel reduce; everything else as before
+    const bool uniformWindows = q.uniformBlocks > 0 && (q.uniformBlocks / 3) % kRedWin == 0;
+    const bool general = !fromQ && !q.stats && q.lagG >= 0 && ctas >= 8 && !uniformWindows;
     const void *fn = fromQ ? (const void *)k_encode<true, false>
-                           : q.stats ? (const void *)k_encode<false, true> : (const void *)k_encode<false, false>;
+                   : general ? (const void *)k_encode<false, false, true>
+                   : q.stats ? (const void *)k_encode<false, true> : (const void *)k_encode<false, false>;
     int perSm = 0;
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, kEncWarps * 32, kEncSmemBytes));
     if (perSm < 1) MNW_PANIC("k_encode does not fit an SM of this device.");

@@ -48,7 +48,7 @@ def write(sym, title, path, specs):
     print(out[0])
 
 
-write("k_encodeILb0ELb0", "k_encode<false,false>", os.path.join(root, "profiles", rnd + "_sass_k_encode.txt"), [
+write("k_encodeILb0ELb0ELb0", "k_encode<false,false>", os.path.join(root, "profiles", rnd + "_sass_k_encode.txt"), [
     (r"UTMALDG", "TMA loads of the issuer warp (cp.async.bulk.tensor.2d -> UTMALDG.2D; the second form carries the evict_first L2 policy of the B reads), each after the stage's mbarrier arrive.expect_tx (SYNCS.ARRIVE.TRANS64)", 7, 2),
     (r"SYNCS\.ARRIVE", "mbarrier arrive (stage handed back / expect_tx)", 3, 2),
     (r"SYNCS\.PHASECHK", "mbarrier try_wait (SYNCS.PHASECHK.TRANS64.TRYWAIT): issuer on `empty`, consumers on `full`", 3, 2),

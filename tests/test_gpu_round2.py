@@ -293,3 +293,46 @@ def test_c_nccl_driver_world_of_one(codec):
         assert float(err[3 * (1 << 16):6 * (1 << 16)].max()) <= 1.0 + 1e-3  # velocities of segment 0: Delta = 1
     finally:
         sh.close()
+
+
+def test_many_fields_of_unequal_size_match_oracle(codec):
+    """the general parallel reduce (k_encode<.., kGeneral>): thousands of fields of random
+    sizes in one batch -- empty ones, single particles, fields of one block, two long ones
+    whose components span many reduce windows -- so that a window of 512 blocks holds
+    hundreds of component boundaries; every field byte for byte, then the round trip"""
+    orc = _oracle.reference() or _oracle.port()
+    rng = np.random.default_rng(5)
+    nf = 2500
+    sizes = rng.integers(0, 3000, nf)
+    sizes[rng.integers(0, nf, 40)] = 0
+    sizes[rng.integers(0, nf, 40)] = 1
+    sizes[[7, 1900]] = [70000, 131072]
+    sizes[-3:] = [0, 5, 0]  # the batch ends in empty fields
+    total = int(sizes.sum())
+    walk = np.cumsum(rng.normal(0.0, 0.01, 3 * total)).astype(np.float32)
+    fields, off = [], 0
+    data = np.empty(3 * total, np.float32)
+    for i, n in enumerate(sizes.tolist()):
+        pos = i % 2 == 0
+        chunk = walk[off:off + 3 * n]
+        data[off:off + 3 * n] = np.mod(chunk + 50.0, 100.0).astype(np.float32) if pos else chunk
+        fields.append((off, n, mc.FIELD_POSN if pos else mc.FIELD_VELC, 1e-3 if pos else 1e-4, 100.0 if pos else 0.0, 900 + i))
+        off += 3 * n
+    data[data >= np.float32(100.0)] = 0.0
+    d_in = torch.from_numpy(data).cuda()
+    d_out = torch.zeros(sum(mc.field_bound(int(n)) for n in sizes), dtype=torch.uint8, device="cuda")
+    d_off = torch.zeros(nf + 1, dtype=torch.int64, device="cuda")
+    descs = mc.make_descs(fields)
+    codec.encode_dev(d_in, descs, nf, d_out, d_off)
+    assert codec.status() == 0
+    offs, out = d_off.cpu().numpy(), d_out.cpu().numpy()
+    for i, (o, n, code, delta, width, seed) in enumerate(fields):
+        want = orc.encode_field(code, data[o:o + 3 * n], delta, width, seed=seed)
+        assert np.array_equal(out[offs[i]:offs[i + 1]], want), "field %d (n = %d)" % (i, n)
+    d_dec = torch.empty_like(d_in)
+    codec.decode_dev(d_out, d_off, descs, nf, d_dec)
+    assert codec.status() == 0
+    err = (d_dec - d_in).abs().cpu().numpy()
+    err = np.minimum(err, np.abs(100.0 - err))
+    tol = np.concatenate([np.full(3 * n, 1e-3 if i % 2 == 0 else 1e-4) for i, n in enumerate(sizes.tolist())])
+    assert (err <= tol * 1.0001).all()
