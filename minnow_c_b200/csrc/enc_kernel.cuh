@@ -435,7 +435,9 @@ constexpr int kRedWarpsGeneral = kRedWarps;  // (22 warps instead of 8: 10.9 aga
 // (f, comp, compEnd) of the component that holds block b (b < nBlocks)
 __device__ __forceinline__ void red_locate(const EncodeParams &p, int64_t b, RedWalk &w) {
     const DevField *fields = p.fields;
-    w.f = find_field(p.nFields, b, [fields](int i) { return fields[i].firstBlock; });
+    // (equal-sized fields: no search -- a dozen dependent loads per window otherwise)
+    if (p.uniformBlocks > 0) w.f = (int)(b / p.uniformBlocks);
+    else w.f = find_field(p.nFields, b, [fields](int i) { return fields[i].firstBlock; });
     const int64_t first = fields[w.f].firstBlock;
     const int nb = fields[w.f].nb;
     w.comp = (int)((b - first) / nb);
@@ -538,37 +540,57 @@ __device__ __forceinline__ void reduce_fold_general(const EncodeParams &p, int l
     w.lo = w.hi = 0xffffffffu;
     red_skip_empty(p, w);
     int pendFrom = w.f;
-    for (int64_t wi = 0; wi < nWin; wi++) {
-        uint4 r0, r1;
+    // 32 windows per round, one lane polling each (a window at a time would be one L2 round
+    // trip per window: thousands of them do not fit in the kernel's time); the records are
+    // merged in order as they arrive
+    for (int64_t w0 = 0; w0 < nWin; w0 += 32) {
+        const int cnt = (int)min((int64_t)32, nWin - w0);
+        uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
+        bool have = false;
+        int done = 0;
         SpinClock clk;
-        while (true) {
-            r1 = ld_relaxed_u4(rec + 2 * wi + 1);
-            r0 = ld_relaxed_u4(rec + 2 * wi);
-            if ((r1.z & kRecValid) && (r0.x | r0.y) != 0u && (!(r1.z & kRecTail) || (r0.z | r0.w) != 0u)) break;
-            if (spin_expired(clk)) {
-                if (lane == 0) spin_timeout(p.error, 6, wi * kRedWin);
-                return;
+        while (done < cnt) {
+            if (lane >= done && lane < cnt && !have) {
+                r1 = ld_relaxed_u4(rec + 2 * (w0 + lane) + 1);
+                r0 = ld_relaxed_u4(rec + 2 * (w0 + lane));
+                have = (r1.z & kRecValid) && (r0.x | r0.y) != 0u && (!(r1.z & kRecTail) || (r0.z | r0.w) != 0u);
             }
-            __nanosleep(200);
-        }
-        __threadfence();
-        w.lo = min(w.lo, r0.x);
-        w.hi = min(w.hi, r0.y);
-        if (r1.z & kRecHeadCloses) {
-            if (lane == 0) {
-                uint32_t *mm = p.minmax + ((int64_t)w.f * 3 + w.comp) * 2;
-                mm[0] = w.lo;
-                mm[1] = w.hi;
+            const unsigned ok = __ballot_sync(kFull, lane < cnt && have);
+            int upto = done;
+            while (upto < cnt && ((ok >> upto) & 1u)) upto++;
+            if (upto > done) __threadfence();
+            for (int i = done; i < upto; i++) {
+                const uint32_t hLo = __shfl_sync(kFull, r0.x, i), hHi = __shfl_sync(kFull, r0.y, i);
+                const uint32_t tLo = __shfl_sync(kFull, r0.z, i), tHi = __shfl_sync(kFull, r0.w, i);
+                const uint32_t fOpen = __shfl_sync(kFull, r1.x, i), cOpen = __shfl_sync(kFull, r1.y, i);
+                const uint32_t flags = __shfl_sync(kFull, r1.z, i);
+                w.lo = min(w.lo, hLo);
+                w.hi = min(w.hi, hHi);
+                if (flags & kRecHeadCloses) {
+                    if (lane == 0) {
+                        uint32_t *mm = p.minmax + ((int64_t)w.f * 3 + w.comp) * 2;
+                        mm[0] = w.lo;
+                        mm[1] = w.hi;
+                    }
+                    w.lo = w.hi = 0xffffffffu;
+                }
+                w.f = (int)fOpen;
+                w.comp = (int)cOpen;
+                if (flags & kRecTail) {
+                    w.lo = tLo;
+                    w.hi = tHi;
+                }
+                red_flush(p, w, pendFrom, lane);  // every field before the open one is complete
             }
-            w.lo = w.hi = 0xffffffffu;
+            if (upto == done) {
+                if (spin_expired(clk)) {
+                    if (lane == 0) spin_timeout(p.error, 6, (w0 + done) * kRedWin);
+                    return;
+                }
+                __nanosleep(200);
+            }
+            done = upto;
         }
-        w.f = (int)r1.x;
-        w.comp = (int)r1.y;
-        if (r1.z & kRecTail) {
-            w.lo = r0.z;
-            w.hi = r0.w;
-        }
-        red_flush(p, w, pendFrom, lane);  // every field before the open one is complete
     }
 }
 

@@ -83,7 +83,9 @@ struct MnwCudaCtx {
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     int smCount = 148;
     int64_t encodeLag = -1;      // groups of 16 blocks between the A and B passes (-1: one field + encodeMargin)
-    int64_t encodeMargin = 128;  // groups of slack so that a field's parameters are ready when its B work starts
+    int64_t encodeMargin = -1;   // groups of slack so that a field's parameters are ready when its B work starts; -1: 128
+                                 // for batches that take the uniform reduce, 384 for the general one (its parameters
+                                 // arrive later: a fence, a record and a fold per window)
                                  // (smaller: B work waits for them; larger: its input has left L2 again)
     void *encodeTiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime (no libcuda link)
     unsigned long long *encStats = nullptr;  // MNWCUDA_ENCODE_STATS
@@ -529,7 +531,9 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     p.in = d_in;
     // the B work of a block trails its A work by one (largest) field plus what can be in flight
     const int64_t fieldGroups = (pl.maxBlocksPerField + kGroupBlocks - 1) / kGroupBlocks;
-    p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + ctx->encodeMargin;
+    const bool uniformWindows = pl.uniformBlocks > 0 && (pl.uniformBlocks / 3) % kRedWin == 0;
+    const int64_t margin = ctx->encodeMargin >= 0 ? ctx->encodeMargin : uniformWindows ? 128 : 384;
+    p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + margin;
     if (p.lagG < fieldGroups + 1) p.lagG = fieldGroups + 1;
     // timing experiments (scripts/enc_only.py; the output of such a call is not a valid stream):
     // "B" = B work alone with the parameters the previous call on this batch left in ctx->quant,
