@@ -45,7 +45,8 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         // CTA 1 of a big launch: its other warps reduce the windows in parallel
         if (blockIdx.x == 1 && p.lagG >= 0 && !kFromQ) {
             if (kGeneral) {
-                if (warp < kRedWarpsGeneral) reduce_windows_general(p, lane, warp);
+                if (warp < kRedWarpsGeneral)
+                    reduce_windows_general(p, reinterpret_cast<uint2 *>(encSmem + kEncRingOff + warp * kEncStageBytes), lane, warp);
             } else if (warp < kRedWarps && reduce_in_parallel(p)) {
                 reduce_windows(p, lane, warp);
             }

@@ -455,7 +455,8 @@ __device__ __forceinline__ void red_advance(const EncodeParams &p, RedWalk &w) {
     }
 }
 
-__device__ __forceinline__ void reduce_windows_general(const EncodeParams &p, int lane, int k) {
+// sm: 4 KiB of shared memory of this warp (CTA 1 has no ring traffic: the stages are free)
+__device__ __forceinline__ void reduce_windows_general(const EncodeParams &p, uint2 *sm, int lane, int k) {
     const int64_t nWin = (p.nBlocks + kRedWin - 1) / kRedWin;
     uint4 *rec = reinterpret_cast<uint4 *>(p.winMM);
     uint4 cur[8];
@@ -483,44 +484,90 @@ __device__ __forceinline__ void reduce_windows_general(const EncodeParams &p, in
         RedWalk w;
         red_locate(p, base, w);
         uint32_t headLo = 0xffffffffu, headHi = 0xffffffffu, tailLo = 0u, tailHi = 0u, flags = kRecValid;
-        int seg = 0;
-        int64_t s0 = base;
-        while (s0 < winEnd) {
-            const int64_t e = min(winEnd, w.compEnd);
-            uint32_t lo = 0xffffffffu, hi = 0xffffffffu;
+        if (w.compEnd >= winEnd) {
+            // the usual case with long fields: the window lies inside one component
 #pragma unroll
             for (int j = 0; j < 8; j++) {
                 const int64_t b0 = base + j * 64 + lane * 2;
-                if (b0 >= s0 && b0 < e) {
-                    lo = min(lo, cur[j].x);
-                    hi = min(hi, cur[j].y);
+                if (b0 < winEnd) {
+                    headLo = min(headLo, cur[j].x);
+                    headHi = min(headHi, cur[j].y);
                 }
-                if (b0 + 1 >= s0 && b0 + 1 < e) {
-                    lo = min(lo, cur[j].z);
-                    hi = min(hi, cur[j].w);
+                if (b0 + 1 < winEnd) {
+                    headLo = min(headLo, cur[j].z);
+                    headHi = min(headHi, cur[j].w);
                 }
             }
-            lo = __reduce_min_sync(kFull, lo);
-            hi = __reduce_min_sync(kFull, hi);
-            const bool closes = e == w.compEnd;
-            if (seg == 0) {
-                headLo = lo;
-                headHi = hi;
-                if (closes) flags |= kRecHeadCloses;
-            } else if (closes) {  // a whole component inside the window
-                if (lane == 0) {
-                    uint32_t *mm = p.minmax + ((int64_t)w.f * 3 + w.comp) * 2;
-                    mm[0] = lo;
-                    mm[1] = hi;
-                }
-            } else {  // it goes on in the next window
-                tailLo = lo;
-                tailHi = hi;
-                flags |= kRecTail;
+            headLo = __reduce_min_sync(kFull, headLo);
+            headHi = __reduce_min_sync(kFull, headHi);
+            if (w.compEnd == winEnd) {
+                flags |= kRecHeadCloses;
+                red_advance(p, w);
             }
-            if (closes) red_advance(p, w);
-            s0 = e;
-            seg++;
+        } else {
+            // Several components: the window goes to shared memory and every lane takes a
+            // component of its own (ordinal 3 f + c; empty fields are empty ranges), round
+            // after round, until one reaches beyond the window's end: that one is open there.
+            // The first component is the head (it may have begun in an earlier window); the
+            // others lie inside the window -- their min/max are final -- or are the tail.
+#pragma unroll
+            for (int j = 0; j < 8; j++) reinterpret_cast<uint4 *>(sm)[32 * j + lane] = cur[j];
+            __syncwarp();
+            const int64_t o0 = (int64_t)w.f * 3 + w.comp, oEnd = (int64_t)p.nFields * 3;
+            bool found = false;
+            w.f = p.nFields;  // (open component if nothing reaches beyond the end: past the last field)
+            w.comp = 0;
+            for (int64_t r0 = o0; r0 < oEnd && !found; r0 += 32) {
+                const int64_t o = r0 + lane;
+                bool beyond = false, isTail = false;
+                uint32_t lo = 0xffffffffu, hi = 0xffffffffu;
+                int f = 0, c = 0;
+                if (o < oEnd) {
+                    f = (int)(o / 3);
+                    c = (int)(o - (int64_t)f * 3);
+                    const int nb = p.fields[f].nb;
+                    const int64_t start = p.fields[f].firstBlock + (int64_t)c * nb, end = start + nb;
+                    beyond = nb > 0 && end > winEnd;  // it holds the block at winEnd, or begins at or after it
+                    const int64_t s0 = max(start, base), e = min(end, winEnd);
+                    for (int64_t b = s0; b < e; b++) {
+                        const uint2 v = sm[b - base];
+                        lo = min(lo, v.x);
+                        hi = min(hi, v.y);
+                    }
+                    if (s0 < e) {
+                        if (o == o0) {
+                            // (picked up below)
+                        } else if (end <= winEnd) {  // a whole component inside the window
+                            uint32_t *mm = p.minmax + o * 2;
+                            mm[0] = lo;
+                            mm[1] = hi;
+                        } else {
+                            isTail = true;
+                        }
+                    }
+                }
+                if (r0 == o0) {  // the head is lane 0's component of the first round
+                    headLo = __shfl_sync(kFull, lo, 0);
+                    headHi = __shfl_sync(kFull, hi, 0);
+                    const bool closes = __shfl_sync(kFull, (int)!beyond, 0) != 0;
+                    if (closes) flags |= kRecHeadCloses;
+                }
+                const unsigned tailMask = __ballot_sync(kFull, isTail);
+                if (tailMask) {
+                    const int src = __ffs(tailMask) - 1;
+                    tailLo = __shfl_sync(kFull, lo, src);
+                    tailHi = __shfl_sync(kFull, hi, src);
+                    flags |= kRecTail;
+                }
+                const unsigned beyondMask = __ballot_sync(kFull, beyond);
+                if (beyondMask) {
+                    const int src = __ffs(beyondMask) - 1;
+                    w.f = __shfl_sync(kFull, f, src);
+                    w.comp = __shfl_sync(kFull, c, src);
+                    found = true;
+                }
+            }
+            __syncwarp();  // (the next window's entries overwrite sm)
         }
         // (w is now the component open at winEnd: the one that holds that block, or past the last field)
         if (lane == 0) {
