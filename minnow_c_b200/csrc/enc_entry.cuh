@@ -34,6 +34,10 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         rc.qHead[0] = rc.qHead[1] = rc.qHead[2] = 0;  // claimed, planned, issued
         rc.qHead[3] = 0xffffffffu;                    // end of the sequence: not known yet
         for (int s = 0; s < kEncStages; s++) rc.uses[s] = 0;
+        if (kGeneral) {  // quant_workers' state (CTA 1 has no ring traffic: the stages are free)
+            volatile int *q = reinterpret_cast<volatile int *>(encSmem + kEncRingOff + kRedWarpsGeneral * kEncStageBytes);
+            q[0] = q[1] = q[2] = 0;
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_proxy_async();
     }
@@ -47,6 +51,8 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             if (kGeneral) {
                 if (warp < kRedWarpsGeneral)
                     reduce_windows_general(p, reinterpret_cast<uint2 *>(encSmem + kEncRingOff + warp * kEncStageBytes), lane, warp);
+                else
+                    quant_workers(p, reinterpret_cast<volatile int *>(encSmem + kEncRingOff + kRedWarpsGeneral * kEncStageBytes), lane);
             } else if (warp < kRedWarps && reduce_in_parallel(p)) {
                 reduce_windows(p, lane, warp);
             }
@@ -66,7 +72,8 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     if (warp == kEncWarps - 1 && lastIsService) {
         if (blockIdx.x == 0) scan_blocks(p, lane);
         else if (p.lagG >= 0 && !kFromQ) {
-            if (kGeneral) reduce_fold_general(p, lane);  // (the host launches it with 8 CTAs or more only)
+            if (kGeneral)  // (the host launches it with 8 CTAs or more only)
+                reduce_fold_general(p, reinterpret_cast<volatile int *>(encSmem + kEncRingOff + kRedWarpsGeneral * kEncStageBytes), lane);
             else if (gridDim.x >= 8 && reduce_in_parallel(p)) reduce_fold(p, lane);
             else reduce_fields(p, lane);
         }

@@ -578,7 +578,36 @@ __device__ __forceinline__ void reduce_windows_general(const EncodeParams &p, ui
     }
 }
 
-__device__ __forceinline__ void reduce_fold_general(const EncodeParams &p, int lane) {
+// The parameters of the fields are worked out by the other warps of CTA 1 (quant_workers):
+// the fold warp only says how many fields are complete -- unless they come one or two at a
+// time (long fields), when it works them out itself at once: a worker's answer is a poll
+// interval later. qState[0] = fields complete (every field below it has all three min/max
+// pairs in p.minmax), qState[1] = next field to hand out, qState[2] = fields below this one
+// were done by the fold warp.
+__device__ __forceinline__ void quant_workers(const EncodeParams &p, volatile int *qState, int lane) {
+    while (true) {
+        int f0 = 0;
+        if (lane == 0) f0 = atomicAdd(const_cast<int *>(qState) + 1, 32);
+        f0 = __shfl_sync(kFull, f0, 0);
+        if (f0 >= p.nFields) return;
+        const int f = f0 + lane;
+        if (f < p.nFields && p.fields[f].nb > 0) {  // (empty fields: k_depth_empty)
+            // a lane waits for its own field only: a long field must not wait for its 31 neighbours
+            SpinClock clk;
+            while (qState[0] <= f) {
+                __nanosleep(200);
+                if (spin_expired(clk)) { spin_timeout(p.error, 10, f); return; }
+            }
+            if (f >= qState[2]) {  // (below qState[2]: the fold warp did it itself)
+                __threadfence();
+                compute_quant(p, f);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+__device__ __forceinline__ void reduce_fold_general(const EncodeParams &p, volatile int *qState, int lane) {
     const int64_t nWin = (p.nBlocks + kRedWin - 1) / kRedWin;
     const uint4 *rec = reinterpret_cast<const uint4 *>(p.winMM);
     RedWalk w;  // the open component
@@ -627,7 +656,17 @@ __device__ __forceinline__ void reduce_fold_general(const EncodeParams &p, int l
                     w.lo = tLo;
                     w.hi = tHi;
                 }
-                red_flush(p, w, pendFrom, lane);  // every field before the open one is complete
+                if (w.f > pendFrom) {  // every field before the open one is complete
+                    const bool self = w.f - pendFrom <= 4;
+                    const int upTo = w.f;
+                    if (self) red_flush(p, w, pendFrom, lane);  // (sets pendFrom = w.f)
+                    if (lane == 0) {
+                        __threadfence();  // (this lane's min/max words, and the window warps' that it has seen)
+                        if (self) qState[2] = upTo;
+                        qState[0] = upTo;
+                    }
+                    pendFrom = upTo;
+                }
             }
             if (upto == done) {
                 if (spin_expired(clk)) {
