@@ -84,8 +84,8 @@ struct MnwCudaCtx {
     int smCount = 148;
     int64_t encodeLag = -1;      // groups of 16 blocks between the A and B passes (-1: one field + encodeMargin)
     int64_t encodeMargin = -1;   // groups of slack so that a field's parameters are ready when its B work starts; -1: 128
-                                 // for batches that take the uniform reduce, 384 for the general one (its parameters
-                                 // arrive later: a fence, a record and a fold per window)
+                                 // to 384 by field size for batches that take the uniform reduce, 384 for the general
+                                 // one (its parameters arrive later: a fence, a record and a fold per window)
                                  // (smaller: B work waits for them; larger: its input has left L2 again)
     void *encodeTiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime (no libcuda link)
     unsigned long long *encStats = nullptr;  // MNWCUDA_ENCODE_STATS
@@ -532,7 +532,12 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
     // the B work of a block trails its A work by one (largest) field plus what can be in flight
     const int64_t fieldGroups = (pl.maxBlocksPerField + kGroupBlocks - 1) / kGroupBlocks;
     const bool uniformWindows = pl.uniformBlocks > 0 && (pl.uniformBlocks / 3) % kRedWin == 0;
-    const int64_t margin = ctx->encodeMargin >= 0 ? ctx->encodeMargin : uniformWindows ? 128 : 384;
+    // (uniform reduce: 128 groups for fields of 2^22 particles -- more and their second read starts to
+    // miss L2 -- up to 384 for smaller ones, whose B work otherwise waits for parameters more often:
+    // 0.40 -> 0.47 of peak at 2^19 particles per field, 0.48 -> 0.53 at 2^21)
+    const int64_t margin = ctx->encodeMargin >= 0 ? ctx->encodeMargin
+                           : !uniformWindows      ? 384
+                                                  : std::max<int64_t>(128, std::min<int64_t>(384, 896 - fieldGroups));
     p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + margin;
     if (p.lagG < fieldGroups + 1) p.lagG = fieldGroups + 1;
     // timing experiments (scripts/enc_only.py; the output of such a call is not a valid stream):
