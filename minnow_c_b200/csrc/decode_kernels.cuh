@@ -489,6 +489,30 @@ __global__ void __launch_bounds__(kDecWarps * 32, 7) k_unpack_dequant(DecodePara
             float4 *d4 = reinterpret_cast<float4 *>(dst) + lane;
 #pragma unroll
             for (int kk = 0; kk < 8; kk++) __stcs(d4 + kk * 32, lds_f4(((kk & 1) ? aOdd : aEven) + kk * 512));
+        } else if (len == kBlockLen) {
+            // A full block whose destination is not 16-byte aligned (particle counts that are not
+            // multiples of four): the same 16-byte reads from the staging area, and each chunk goes
+            // out as the widest stores its address allows -- two 8-byte ones, or 4 + 8 + 4.
+            const uint32_t r0 = lane >> 3, jj = lane & 7;
+            const uint32_t aEven = (uint32_t)__cvta_generic_to_shared(st) + ((r0 * 8 + (jj ^ r0)) << 4);
+            const uint32_t aOdd = aEven ^ 64u;
+            float *d1 = dst + lane * 4;
+            if (((uintptr_t)dst & 7) == 0) {
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) {
+                    const float4 v = lds_f4(((kk & 1) ? aOdd : aEven) + kk * 512);
+                    __stcs(reinterpret_cast<float2 *>(d1 + kk * 128), make_float2(v.x, v.y));
+                    __stcs(reinterpret_cast<float2 *>(d1 + kk * 128 + 2), make_float2(v.z, v.w));
+                }
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) {
+                    const float4 v = lds_f4(((kk & 1) ? aOdd : aEven) + kk * 512);
+                    __stcs(d1 + kk * 128, v.x);
+                    __stcs(reinterpret_cast<float2 *>(d1 + kk * 128 + 1), make_float2(v.y, v.z));
+                    __stcs(d1 + kk * 128 + 3, v.w);
+                }
+            }
         } else {
 #pragma unroll 4
             for (int kk = 0; kk < 32; kk++) {

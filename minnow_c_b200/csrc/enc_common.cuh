@@ -94,6 +94,7 @@ struct EncodeParams {
     uint4 *tbl;            // [nBlocks] First, MinDelta, Width of the block (k_tables adds Offset16)
     uint64_t *blkMM;       // [nBlocks, padded to kRedWin] ord(min) | ~ord(max) << 32 of the block, 0 = not there yet
     uint64_t *fq;          // [nFields][3][2] published parameters of a component (see publish_quant)
+    int offGrid;           // host: some block of the batch does not start on the 128-byte grid (which kernel to launch)
     uint64_t *winMM;       // [nBlocks / kRedWin] the same per reduce window (parallel reduce), 0 = not there yet
     uint32_t *scratch;     // [CTAs][kEncConsumers][kFifo][kSlotWords] packed blocks waiting for their offset
     int64_t tmaShift;      // floats between the tensor map's 128-byte aligned base and `in`; <0: no TMA

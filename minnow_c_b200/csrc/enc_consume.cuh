@@ -163,7 +163,9 @@ __device__ __forceinline__ bool place_oldest(const EncodeParams &p, ParkFifo &ff
 // B work on block d.blk
 // ---------------------------------------------------------------------------
 // (false: a wait timed out, the caller leaves the kernel; the stage has been handed back)
-template <bool kFromQ, bool kStats>
+// (kVec: full blocks off the 16-byte grid are staged with vector loads -- the general kernel only: the
+// kernel of the uniform batches stays what it is)
+template <bool kFromQ, bool kStats, bool kVec = false>
 __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, float *stage, const RingCtrl &rc,
                                         int s, ParkFifo &ff, int lane) {
     const int64_t blk = d.blk;
@@ -188,14 +190,18 @@ __device__ __forceinline__ bool b_block(const EncodeParams &p, WorkDesc &d, floa
             // ragged or unaligned block: plain loads into the stage, same swizzled layout
             const DevField *fdp = p.fields + d.f;
             const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
-            const float fill = __ldg(src);
+            if (kVec && len == kBlockLen) {
+                stage_full_unaligned(src, stage, lane);  // (a full block off the 16-byte grid: vector loads)
+            } else {
+                const float fill = __ldg(src);
 #pragma unroll 4
-            for (int k = 0; k < 32; k++) {
-                const int e = k * 32 + lane;
-                const float x = e < len ? __ldg(src + e) : fill;
-                stage[swz_chunk(e >> 5, (e >> 2) & 7) * 4 + (e & 3)] = x;
+                for (int k = 0; k < 32; k++) {
+                    const int e = k * 32 + lane;
+                    const float x = e < len ? __ldg(src + e) : fill;
+                    stage[swz_chunk(e >> 5, (e >> 2) & 7) * 4 + (e & 3)] = x;
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
         // the lane's 32 values to registers, the stage back to the producer
         load_block32(stage, lane, q);

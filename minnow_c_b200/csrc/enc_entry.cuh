@@ -133,14 +133,14 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             continue;
         }
         if (d.kind == kWorkA) {
-            a_block(p, d, stage, lane);
+            a_block<kGeneral>(p, d, stage, lane);
             release_stage(rc, s, false, lane);
             if (kStats) {
                 tA += clock64() - c1;
                 nA++;
             }
         } else if (d.kind == kWorkB) {
-            if (!b_block<kFromQ, kStats>(p, d, stage, rc, s, ff, lane)) {
+            if (!b_block<kFromQ, kStats, kGeneral>(p, d, stage, rc, s, ff, lane)) {
                 drain = true;  // (b_block hands its stage back before anything that can time out)
                 continue;
             }

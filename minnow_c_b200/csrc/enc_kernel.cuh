@@ -700,6 +700,7 @@ __device__ __forceinline__ void minmax_stage(const float4 *st, int lane, const U
     }
 }
 
+template <bool kVec = false>
 __device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d, const float *stage, int lane) {
     const bool isPos = d.flags & kDescPos;
     Unwrap uw;
@@ -734,11 +735,32 @@ __device__ __forceinline__ void a_block(const EncodeParams &p, const WorkDesc &d
     } else {
         const DevField *fdp = p.fields + d.f;
         const float *src = p.in + fdp->ioOff + (int64_t)d.comp * fdp->n + (int64_t)d.b * kBlockLen;
-        for (int i = lane; i < d.len; i += 32) {
-            float u = __ldg(src + i);
-            if (isPos) u = unwrap_t(u, uw);
-            lo = fminf(lo, u);
-            hi = fmaxf(hi, u);
+        bool done = false;
+        if (kVec && d.len == kBlockLen) {
+            // a full block off the 16-byte grid: vector loads, and the extrema rule of the staged path
+            float lohi[2];
+            minmax_full_unaligned(src, lane, lohi);
+            lo = lohi[0];
+            hi = lohi[1];
+            const bool split = isPos && ((lo < uw.tHi && !(hi < uw.tHi)) || (lo < uw.tLo && !(hi < uw.tLo)) || !(lo <= hi));
+            if (!__any_sync(kFull, split)) {
+                if (isPos) {
+                    lo = unwrap_t(lo, uw);
+                    hi = unwrap_t(hi, uw);
+                }
+                done = true;
+            } else {
+                lo = __int_as_float(0x7f800000);
+                hi = __int_as_float(0xff800000);
+            }
+        }
+        if (!done) {
+            for (int i = lane; i < d.len; i += 32) {
+                float u = __ldg(src + i);
+                if (isPos) u = unwrap_t(u, uw);
+                lo = fminf(lo, u);
+                hi = fmaxf(hi, u);
+            }
         }
     }
     const uint32_t olo = __reduce_min_sync(kFull, ord_from_float(lo));

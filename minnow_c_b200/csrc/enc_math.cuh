@@ -71,6 +71,51 @@ __device__ __forceinline__ float unwrap_t(float v, const Unwrap &u) {
 // becomes fmin against the largest index (an integer, so trunc commutes).
 // s >= 0 always: x0 is the minimum of the very same unwrapped values.
 
+// Chunk c = kk * 32 + lane (elements 4c .. 4c+3) of a full block that does not start on a
+// 16-byte boundary (particle counts that are not multiples of four: the TMA cannot fetch
+// it), with the widest loads its address allows -- two 8-byte ones, or 4 + 8 + 4.
+__device__ __forceinline__ float4 ldg_chunk_unaligned(const float *src, int c, bool by8) {
+    const float *s = src + c * 4;
+    float4 v;
+    if (by8) {
+        const float2 a = __ldg(reinterpret_cast<const float2 *>(s)), b = __ldg(reinterpret_cast<const float2 *>(s + 2));
+        v = make_float4(a.x, a.y, b.x, b.y);
+    } else {
+        const float a = __ldg(s);
+        const float2 b = __ldg(reinterpret_cast<const float2 *>(s + 1));
+        const float d = __ldg(s + 3);
+        v = make_float4(a, b.x, b.y, d);
+    }
+    return v;
+}
+
+// ... into the stage, in the swizzled layout the TMA would have produced (out of line: this is
+// the path of unaligned batches only, and the kernel is sensitive to the size of its hot code)
+__device__ __noinline__ void stage_full_unaligned(const float *src, float *stage, int lane) {
+    const bool by8 = ((uintptr_t)src & 7) == 0;
+    float4 *st = reinterpret_cast<float4 *>(stage);
+#pragma unroll
+    for (int kk = 0; kk < 8; kk++) {
+        const int c = kk * 32 + lane;
+        st[swz_chunk(c >> 3, c & 7)] = ldg_chunk_unaligned(src, c, by8);
+    }
+    __syncwarp();
+}
+
+// ... or straight into the extrema (A work: nothing else needs the values)
+__device__ __noinline__ void minmax_full_unaligned(const float *src, int lane, float *lohi) {
+    const bool by8 = ((uintptr_t)src & 7) == 0;
+    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+#pragma unroll
+    for (int kk = 0; kk < 8; kk++) {
+        const float4 v = ldg_chunk_unaligned(src, kk * 32 + lane, by8);
+        lo = fminf(fminf(lo, v.x), fminf(v.y, fminf(v.z, v.w)));
+        hi = fmaxf(fmaxf(hi, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+    }
+    lohi[0] = lo;
+    lohi[1] = hi;
+}
+
 // the lane's 32 consecutive values of a staged block (128-byte swizzle), as bit patterns
 __device__ __forceinline__ void load_block32(const float *stage, int lane, uint32_t (&q)[kChunk]) {
 #pragma unroll

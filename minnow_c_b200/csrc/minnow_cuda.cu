@@ -354,6 +354,7 @@ struct Plan {
     int64_t maxBlocksPerField = 0;
     int64_t floatEnd = 0;  // one past the last input float any field refers to
     bool hasEmpty = false;
+    bool aligned32 = true;  // every component of every field starts a multiple of 32 floats from the batch's base
 };
 
 int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
@@ -384,6 +385,7 @@ int build_plan(const MnwFieldDesc *h, int64_t nFields, Plan &pl) {
         if (3 * (int64_t)f.nb > pl.maxBlocksPerField) pl.maxBlocksPerField = 3 * (int64_t)f.nb;
         if (d.Offset + 3ll * d.ParticleLen > pl.floatEnd) pl.floatEnd = d.Offset + 3ll * d.ParticleLen;
         if (d.ParticleLen == 0) pl.hasEmpty = true;
+        if ((d.Offset & 31) || (d.ParticleLen & 31)) pl.aligned32 = false;
         if (d.ParticleLen != h[0].ParticleLen || d.ParticleLen == 0) uniform = false;
     }
     if (uniform && nFields > 0) {
@@ -482,7 +484,9 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     // big batches whose components are not whole reduce windows (fields of unequal size): the
     // instantiation with the general parallel reduce; everything else as before
     const bool uniformWindows = q.uniformBlocks > 0 && (q.uniformBlocks / 3) % kRedWin == 0;
-    const bool general = !fromQ && !q.stats && q.lagG >= 0 && ctas >= 8 && !uniformWindows;
+    // ... and batches with blocks off the 128-byte grid (its A and B work fetch those with vector loads)
+    const bool offGrid = q.offGrid || (q.tmaShift & 31) != 0;
+    const bool general = !fromQ && !q.stats && q.lagG >= 0 && ctas >= 8 && (!uniformWindows || offGrid);
     const void *fn = fromQ ? (const void *)k_encode<true, false>
                    : general ? (const void *)k_encode<false, false, true>
                    : q.stats ? (const void *)k_encode<false, true> : (const void *)k_encode<false, false>;
@@ -540,6 +544,7 @@ extern "C" int mnwcuda_EncodeFieldsDev(MnwCudaCtx *ctx, const float *d_in, const
                                                   : std::max<int64_t>(128, std::min<int64_t>(384, 896 - fieldGroups));
     p.lagG = ctx->encodeLag >= 0 ? ctx->encodeLag : fieldGroups + margin;
     if (p.lagG < fieldGroups + 1) p.lagG = fieldGroups + 1;
+    p.offGrid = pl.aligned32 ? 0 : 1;
     // timing experiments (scripts/enc_only.py; the output of such a call is not a valid stream):
     // "B" = B work alone with the parameters the previous call on this batch left in ctx->quant,
     // "A" = A work alone (MNWCUDA_DBG 64 makes the planner skip the B slots and the scan warp leave)
