@@ -66,7 +66,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         return;
     }
     if (warp == 1) {
-        issuer<kStats>(p, &tmap, encSmem, rc, lane);
+        issuer<kStats, kGeneral>(p, &tmap, encSmem, rc, lane);
         return;
     }
     if (warp == kEncWarps - 1 && lastIsService) {

@@ -279,7 +279,9 @@ __device__ __forceinline__ void planner(const EncodeParams &p, const CUtensorMap
 // block holds one longer than an A block). Nothing else happens on this path: the
 // descriptors were worked out ahead of time by the planner.
 // ---------------------------------------------------------------------------
-template <bool kStats>
+// (kPrefetch: a block the TMA cannot fetch -- off the 16-byte grid -- is at least asked into L2 here, a ring's
+// depth before its consumer loads it by hand; the general kernel only)
+template <bool kStats, bool kPrefetch = false>
 __device__ __forceinline__ void issuer(const EncodeParams &p, const CUtensorMap *map, uint8_t *smem,
                                        const RingCtrl &rc, int lane) {
     // A reads carry no cache hint, B reads are evict_first: with the B work ~56 MB of
@@ -321,6 +323,8 @@ __device__ __forceinline__ void issuer(const EncodeParams &p, const CUtensorMap 
                     if (kind == kWorkA) tma_load_block_plain(smem + kEncRingOff + s * kEncStageBytes, map, row, rc.full + s);
                     else tma_load_block(smem + kEncRingOff + s * kEncStageBytes, map, row, rc.full + s, drop);
                 } else {
+                    if (kPrefetch && (kind == kWorkA || kind == kWorkB) && p.tmaShift >= 0 && row >= 0 && (int64_t)row + 32 <= p.tmaRows)
+                        tma_prefetch_block(map, row);
                     mbar_arrive(rc.full + s);
                 }
                 filled = true;
