@@ -16,7 +16,9 @@ namespace mnw {
 // reduce, enc_kernel.cuh) -- an instantiation of its own so that the kernel of the uniform
 // batches stays exactly what it is (its time moves with anything that changes its service
 // warps' code).
-template <bool kFromQ, bool kStats, bool kGeneral = false>
+// kOffGrid (with kGeneral): batches with blocks off the 128-byte grid -- vector loads by hand in the A and B
+// work, L2 prefetch by the issuer. Again an instantiation of its own: that code costs the others 2 %.
+template <bool kFromQ, bool kStats, bool kGeneral = false, bool kOffGrid = false>
 __global__ void __launch_bounds__(kEncWarps * 32, 1)
 k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) uint8_t encSmem[];
@@ -66,7 +68,7 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
         return;
     }
     if (warp == 1) {
-        issuer<kStats, kGeneral>(p, &tmap, encSmem, rc, lane);
+        issuer<kStats, kOffGrid>(p, &tmap, encSmem, rc, lane);
         return;
     }
     if (warp == kEncWarps - 1 && lastIsService) {
@@ -133,14 +135,14 @@ k_encode(EncodeParams p, const __grid_constant__ CUtensorMap tmap) {
             continue;
         }
         if (d.kind == kWorkA) {
-            a_block<kGeneral>(p, d, stage, lane);
+            a_block<kOffGrid>(p, d, stage, lane);
             release_stage(rc, s, false, lane);
             if (kStats) {
                 tA += clock64() - c1;
                 nA++;
             }
         } else if (d.kind == kWorkB) {
-            if (!b_block<kFromQ, kStats, kGeneral>(p, d, stage, rc, s, ff, lane)) {
+            if (!b_block<kFromQ, kStats, kOffGrid>(p, d, stage, rc, s, ff, lane)) {
                 drain = true;  // (b_block hands its stage back before anything that can time out)
                 continue;
             }

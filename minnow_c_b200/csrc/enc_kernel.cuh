@@ -429,7 +429,7 @@ __device__ __forceinline__ void reduce_fold(const EncodeParams &p, int lane) {
 // The window warp's plain stores to p.minmax are ordered before its record by a fence, and
 // the fold warp fences after it has seen the record.
 // ---------------------------------------------------------------------------
-constexpr uint32_t kRecValid = 0x80000000u, kRecHeadCloses = 1u, kRecTail = 2u;
+constexpr uint32_t kRecValid = 0x80000000u, kRecHeadCloses = 1u, kRecTail = 2u, kRecWrote = 4u;  // kRecWrote: p.minmax words too
 constexpr int kRedWarpsGeneral = kRedWarps;  // (22 warps instead of 8: 10.9 against 8.3 ms on 40 000 small fields -- more pollers, not more progress)
 
 // (f, comp, compEnd) of the component that holds block b (b < nBlocks)
@@ -541,6 +541,7 @@ __device__ __forceinline__ void reduce_windows_general(const EncodeParams &p, ui
                             uint32_t *mm = p.minmax + o * 2;
                             mm[0] = lo;
                             mm[1] = hi;
+                            __threadfence();  // (before this window's record)
                         } else {
                             isTail = true;
                         }
@@ -567,11 +568,11 @@ __device__ __forceinline__ void reduce_windows_general(const EncodeParams &p, ui
                     found = true;
                 }
             }
-            __syncwarp();  // (the next window's entries overwrite sm)
+            flags |= kRecWrote;
+            __syncwarp();  // (the next window's entries overwrite sm; the lanes' fences are behind them)
         }
         // (w is now the component open at winEnd: the one that holds that block, or past the last field)
         if (lane == 0) {
-            __threadfence();
             st_relaxed_u4(rec + 2 * wi, make_uint4(headLo, headHi, tailLo, tailHi));
             st_relaxed_u4(rec + 2 * wi + 1, make_uint4((uint32_t)w.f, (uint32_t)w.comp, flags, 0u));
         }
@@ -634,12 +635,12 @@ __device__ __forceinline__ void reduce_fold_general(const EncodeParams &p, volat
             const unsigned ok = __ballot_sync(kFull, lane < cnt && have);
             int upto = done;
             while (upto < cnt && ((ok >> upto) & 1u)) upto++;
-            if (upto > done) __threadfence();
             for (int i = done; i < upto; i++) {
                 const uint32_t hLo = __shfl_sync(kFull, r0.x, i), hHi = __shfl_sync(kFull, r0.y, i);
                 const uint32_t tLo = __shfl_sync(kFull, r0.z, i), tHi = __shfl_sync(kFull, r0.w, i);
                 const uint32_t fOpen = __shfl_sync(kFull, r1.x, i), cOpen = __shfl_sync(kFull, r1.y, i);
                 const uint32_t flags = __shfl_sync(kFull, r1.z, i);
+                if (flags & kRecWrote) __threadfence();  // (min/max words of the components inside that window)
                 w.lo = min(w.lo, hLo);
                 w.hi = min(w.hi, hHi);
                 if (flags & kRecHeadCloses) {

@@ -204,6 +204,7 @@ extern "C" MnwCudaCtx *mnwcuda_Create(int device) {
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(k_encode<false, false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kEncSmemBytes));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -486,9 +487,9 @@ void launch_encode(MnwCudaCtx *ctx, const EncodeParams &p, int64_t floatEnd, boo
     const bool uniformWindows = q.uniformBlocks > 0 && (q.uniformBlocks / 3) % kRedWin == 0;
     // ... and batches with blocks off the 128-byte grid (its A and B work fetch those with vector loads)
     const bool offGrid = q.offGrid || (q.tmaShift & 31) != 0;
-    const bool general = !fromQ && !q.stats && q.lagG >= 0 && ctas >= 8 && (!uniformWindows || offGrid);
+    const bool general = !fromQ && !q.stats && q.lagG >= 0 && ctas >= 8 && (!uniformWindows || offGrid || (q.dbg & 128));  // (128: experiment)
     const void *fn = fromQ ? (const void *)k_encode<true, false>
-                   : general ? (const void *)k_encode<false, false, true>
+                   : general ? (offGrid ? (const void *)k_encode<false, false, true, true> : (const void *)k_encode<false, false, true>)
                    : q.stats ? (const void *)k_encode<false, true> : (const void *)k_encode<false, false>;
     int perSm = 0;
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, kEncWarps * 32, kEncSmemBytes));
