@@ -336,7 +336,10 @@ __device__ __forceinline__ void reduce_fields(const EncodeParams &p, int lane) {
 // (ord(min) | ~ord(max) << 32, never zero), and one more warp folds those words in
 // order, 32 windows per load, and finishes the components.
 // ---------------------------------------------------------------------------
-constexpr int kRedWarps = 8;
+#ifndef MNW_RED_WARPS
+#define MNW_RED_WARPS 8
+#endif
+constexpr int kRedWarps = MNW_RED_WARPS;
 
 __device__ __forceinline__ bool reduce_in_parallel(const EncodeParams &p) {
     return p.uniformBlocks > 0 && (p.uniformBlocks / 3) % kRedWin == 0 && p.winMM != nullptr;
